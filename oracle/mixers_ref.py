@@ -1,0 +1,248 @@
+"""Oracle (CPU restatement) of the reference's spectral token-mixer path.
+
+TEST INFRASTRUCTURE ONLY -- see ``oracle/__init__.py``.
+
+What it restates
+----------------
+The reference (Biblbrox/ViT-Spectre-Experiments @ fa0d82be) has no module that
+composes ``rfft2 -> learned complex filter -> irfft2``;
+the "reference path" is the composition of the reference's own primitives and
+conventions placed in its ``mix_layer`` slot:
+
+* slot + call:   ``spectre_vit/models/spectre/spectre.py:50`` (construction),
+                 ``:66`` (``x = self.norm1(self.mix_layer(x)) + x``);
+                 tokens are ``[B, 1 + H*W, E]`` with CLS first (``:151-152,182,198``)
+* 2-D FFT conv.: ``torch.fft.rfft2(x, norm="ortho")`` at ``spectre.py:136``;
+                 2-D FFT over the token grid as the mixer at
+                 ``spectre_vit/repl/orthogonal_permut.py:23-28``
+* 1-D FFT conv.: ``torch.fft.rfft(x, dim=-1).real`` at ``spectre_vit/modules/spectre.py:14``
+* Haar / zero:   ``DWTForward(J=3, wave="haar", mode="zero")`` at
+                 ``spectre_vit/repl/dwt_experiments.py:9,56``
+
+Pinning status
+--------------
+* FFT mixer: PINNED.  ``torch.fft`` (the reference's arithmetic) is executed
+  directly, and an independent float64 direct-DFT restatement
+  (:func:`rfft2_ortho_np`, :func:`fft_mix_np`) is checked against (a) torch.fft
+  and (b) golden vectors produced by importing the reference's own
+  ``SpectralPatchEmbed`` / ``FFT`` / ``SpectreViT`` classes
+  (``oracle/make_golden.py`` -> ``tests/golden/*.npz``).
+* Haar DWT mixer: PARITY UNPINNED.  The arithmetic would live in
+  ``pytorch-wavelets>=1.3.0`` / ``ptwt>=1.0.1`` / ``pywavelets>=1.9.0``
+  (``pyproject.toml:11,23,27,28``), none vendored under the reference, none
+  installed here, no version pinned (uv.lock is git-ignored) and the reference
+  holds no test or fixture at that boundary.  The restatement follows the
+  published orthonormal Haar analysis filters ``lo=[1,1]/sqrt2``,
+  ``hi=[1,-1]/sqrt2`` and is checked against an explicit conv filter bank and
+  perfect reconstruction only.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+# --------------------------------------------------------------------------
+# FFT mixer
+# --------------------------------------------------------------------------
+
+
+def as_complex_filter(filt: torch.Tensor) -> torch.Tensor:
+    """``[H, Wh, E, 2]`` real parameter -> ``[H, Wh, E]`` complex view."""
+    if torch.is_complex(filt):
+        return filt
+    return torch.view_as_complex(filt.contiguous())
+
+
+def fft_mix_ref(x: torch.Tensor, filt: torch.Tensor, H: int, W: int) -> torch.Tensor:
+    """y = cat(cls, irfft2(rfft2(grid) * filt)) with the reference's ortho norm.
+
+    x: ``[B, 1+H*W, E]`` fp32/fp64; filt: complex ``[H, W//2+1, E]`` or real
+    ``[H, W//2+1, E, 2]``.  Conventions: ``spectre.py:136`` (``norm="ortho"``),
+    grid = tokens 1.. reshaped ``[B, H, W, E]`` (``spectre.py:151-152``).
+    """
+    B, T, E = x.shape
+    assert T == 1 + H * W
+    f = as_complex_filter(filt)
+    g = x[:, 1:].reshape(B, H, W, E)
+    X = torch.fft.rfft2(g, dim=(1, 2), norm="ortho")
+    y = torch.fft.irfft2(X * f, s=(H, W), dim=(1, 2), norm="ortho")
+    return torch.cat([x[:, :1], y.reshape(B, H * W, E)], dim=1)
+
+
+def fft_mix_bwd_ref(dy: torch.Tensor, x: torch.Tensor, filt: torch.Tensor, H: int, W: int):
+    """Closed-form backward of :func:`fft_mix_ref`.
+
+    Returns ``(dx [B,T,E], dfilt [H,Wh,E,2])``.  ``dfilt`` is the gradient w.r.t.
+    the real ``[H,Wh,E,2]`` parameter, i.e. (Re, Im) of
+    ``sum_b conj(X_b) * (c * DY_b)`` with ``c[kw]=1`` for kw=0 and (W even)
+    kw=W/2, else 2.
+    """
+    B, T, E = x.shape
+    f = as_complex_filter(filt)
+    Wh = W // 2 + 1
+    DY = torch.fft.rfft2(dy[:, 1:].reshape(B, H, W, E), dim=(1, 2), norm="ortho")
+    X = torch.fft.rfft2(x[:, 1:].reshape(B, H, W, E), dim=(1, 2), norm="ortho")
+    dxg = torch.fft.irfft2(f.conj() * DY, s=(H, W), dim=(1, 2), norm="ortho")
+    c = torch.full((Wh,), 2.0, dtype=x.dtype)
+    c[0] = 1.0
+    if W % 2 == 0:
+        c[-1] = 1.0
+    dfc = (X.conj() * DY * c.view(1, 1, Wh, 1)).sum(0)
+    dx = torch.cat([dy[:, :1], dxg.reshape(B, H * W, E)], dim=1)
+    return dx, torch.view_as_real(dfc).contiguous()
+
+
+def rfft2_ortho_np(g: np.ndarray) -> np.ndarray:
+    """Independent float64 direct-DFT restatement of
+    ``torch.fft.rfft2(g, dim=(-2,-1), norm="ortho")`` (no FFT library)."""
+    g = np.asarray(g, dtype=np.float64)
+    H, W = g.shape[-2:]
+    Wh = W // 2 + 1
+    Fw = np.exp(-2j * np.pi * np.outer(np.arange(W), np.arange(Wh)) / W)      # [W, Wh]
+    Fh = np.exp(-2j * np.pi * np.outer(np.arange(H), np.arange(H)) / H)       # [kh, h]
+    rows = g @ Fw                                                             # [..., H, Wh]
+    return np.einsum("kh,...hw->...kw", Fh, rows) / math.sqrt(H * W)
+
+
+def irfft2_ortho_np(Z: np.ndarray, H: int, W: int) -> np.ndarray:
+    """Direct-DFT restatement of ``torch.fft.irfft2(Z, s=(H,W), norm="ortho")``
+    for a possibly non-Hermitian ``Z`` ``[..., H, Wh]``: complex inverse along
+    H, then C2R along W which ignores Im of column 0 and (W even) column W/2."""
+    Z = np.asarray(Z, dtype=np.complex128)
+    Wh = W // 2 + 1
+    Fh = np.exp(2j * np.pi * np.outer(np.arange(H), np.arange(H)) / H)        # [h, kh]
+    cols = np.einsum("hk,...kw->...hw", Fh, Z)                                # [..., H, Wh]
+    c = np.full(Wh, 2.0)
+    c[0] = 1.0
+    if W % 2 == 0:
+        c[-1] = 1.0
+    cols = cols.copy()
+    cols[..., 0] = cols[..., 0].real
+    if W % 2 == 0:
+        cols[..., -1] = cols[..., -1].real
+    Fw = np.exp(2j * np.pi * np.outer(np.arange(Wh), np.arange(W)) / W)       # [kw, w]
+    return ((cols * c) @ Fw).real / math.sqrt(H * W)
+
+
+def fft_mix_np(x: np.ndarray, filt: np.ndarray, H: int, W: int) -> np.ndarray:
+    """Float64 direct-DFT version of :func:`fft_mix_ref`.  ``filt`` complex ``[H,Wh,E]``."""
+    x = np.asarray(x, dtype=np.float64)
+    B, T, E = x.shape
+    g = x[:, 1:].reshape(B, H, W, E).transpose(0, 3, 1, 2)                    # [B,E,H,W]
+    X = rfft2_ortho_np(g)
+    Z = X * np.asarray(filt).transpose(2, 0, 1)[None]
+    y = irfft2_ortho_np(Z, H, W).transpose(0, 2, 3, 1).reshape(B, H * W, E)
+    return np.concatenate([x[:, :1], y], axis=1)
+
+
+# --------------------------------------------------------------------------
+# Haar DWT mixer (rows A5 / A6) -- parity unpinned, see module docstring
+# --------------------------------------------------------------------------
+
+
+def haar2d(g: torch.Tensor) -> torch.Tensor:
+    """Single-level orthonormal 2-D Haar analysis.  g ``[B,H,W,E]`` (H, W even)
+    -> ``[B,4,H/2,W/2,E]`` ordered (LL, W-low/H-high, W-high/H-low, HH)."""
+    a, b = g[:, 0::2, 0::2], g[:, 0::2, 1::2]
+    c, d = g[:, 1::2, 0::2], g[:, 1::2, 1::2]
+    return torch.stack(
+        [(a + b + c + d) / 2, (a + b - c - d) / 2, (a - b + c - d) / 2, (a - b - c + d) / 2], dim=1
+    )
+
+
+def ihaar2d(s4: torch.Tensor) -> torch.Tensor:
+    """Inverse of :func:`haar2d` (same butterflies; the 4x4 block matrix is
+    orthogonal and symmetric)."""
+    ll, s1, s2, hh = s4.unbind(1)
+    a = (ll + s1 + s2 + hh) / 2
+    b = (ll + s1 - s2 - hh) / 2
+    c = (ll - s1 + s2 - hh) / 2
+    d = (ll - s1 - s2 + hh) / 2
+    B, h, w, E = a.shape
+    out = a.new_empty(B, 2 * h, 2 * w, E)
+    out[:, 0::2, 0::2], out[:, 0::2, 1::2] = a, b
+    out[:, 1::2, 0::2], out[:, 1::2, 1::2] = c, d
+    return out
+
+
+def dwt_mix_ref(x: torch.Tensor, w: torch.Tensor, H: int, W: int) -> torch.Tensor:
+    """y = cat(cls, IDWT(w * DWT(grid))).  w real ``[4, H/2, W/2, E]``."""
+    B, T, E = x.shape
+    assert T == 1 + H * W and H % 2 == 0 and W % 2 == 0
+    y = ihaar2d(haar2d(x[:, 1:].reshape(B, H, W, E)) * w)
+    return torch.cat([x[:, :1], y.reshape(B, H * W, E)], dim=1)
+
+
+def dwt_mix_bwd_ref(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, H: int, W: int):
+    """Closed-form backward (row A6): dx = IDWT(w * DWT(dy)); dw = sum_b DWT(x) * DWT(dy)."""
+    B, T, E = x.shape
+    DY = haar2d(dy[:, 1:].reshape(B, H, W, E))
+    X = haar2d(x[:, 1:].reshape(B, H, W, E))
+    dxg = ihaar2d(DY * w)
+    dx = torch.cat([dy[:, :1], dxg.reshape(B, H * W, E)], dim=1)
+    return dx, (X * DY).sum(0)
+
+
+def haar2d_filterbank(g: torch.Tensor) -> torch.Tensor:
+    """The same transform written as the published pywt/pytorch_wavelets Haar
+    filter bank (``lo=[1,1]/sqrt2``, ``hi=[1,-1]/sqrt2``, stride 2, no padding
+    needed for even sizes under ``mode="zero"``) -- used only to cross-check
+    :func:`haar2d`."""
+    r = 1.0 / math.sqrt(2.0)
+    lo_w = (g[:, :, 0::2] + g[:, :, 1::2]) * r
+    hi_w = (g[:, :, 0::2] - g[:, :, 1::2]) * r
+    ll = (lo_w[:, 0::2] + lo_w[:, 1::2]) * r
+    lh = (lo_w[:, 0::2] - lo_w[:, 1::2]) * r      # low along W, high along H
+    hl = (hi_w[:, 0::2] + hi_w[:, 1::2]) * r      # high along W, low along H
+    hh = (hi_w[:, 0::2] - hi_w[:, 1::2]) * r
+    return torch.stack([ll, lh, hl, hh], dim=1)
+
+
+# --------------------------------------------------------------------------
+# nn.Module occupants of the mix_layer slot, pure torch (CPU baseline / tests)
+# --------------------------------------------------------------------------
+
+
+class OracleFFTMix(nn.Module):
+    """Pure-torch occupant of ``mix_layer`` (ctor contract of ``MHPermutMix``,
+    ``spectre_vit/models/spectre/layers.py:54``).  Parameter name/shape match
+    the product module so state dicts are interchangeable."""
+
+    def __init__(self, embed_dim, token_dim, num_heads, out_channels, *, grid=None):
+        super().__init__()
+        assert out_channels == embed_dim
+        if grid is None:
+            s = math.isqrt(token_dim - 1)
+            grid = (s, s)
+        self.grid = tuple(grid)
+        H, W = self.grid
+        assert H * W + 1 == token_dim
+        f = torch.zeros(H, W // 2 + 1, embed_dim, 2)
+        f[..., 0] = 1.0
+        self.filter = nn.Parameter(f + 0.02 * torch.randn_like(f))
+
+    def forward(self, x):
+        H, W = self.grid
+        dt = x.dtype
+        return fft_mix_ref(x.float(), self.filter.float(), H, W).to(dt)
+
+
+class OracleDWTMix(nn.Module):
+    def __init__(self, embed_dim, token_dim, num_heads, out_channels, *, grid=None):
+        super().__init__()
+        assert out_channels == embed_dim
+        if grid is None:
+            s = math.isqrt(token_dim - 1)
+            grid = (s, s)
+        self.grid = tuple(grid)
+        H, W = self.grid
+        assert H * W + 1 == token_dim and H % 2 == 0 and W % 2 == 0
+        self.weight = nn.Parameter(1.0 + 0.02 * torch.randn(4, H // 2, W // 2, embed_dim))
+
+    def forward(self, x):
+        H, W = self.grid
+        dt = x.dtype
+        return dwt_mix_ref(x.float(), self.weight.float(), H, W).to(dt)
