@@ -1,0 +1,96 @@
+/* spectre_b200.h -- C ABI of the B200 (sm_100a) spectral token-mixer kernels.
+ *
+ * This is the drop-in boundary for the reference's `mix_layer` slot
+ *   spectre_vit/models/spectre/spectre.py:50   self.mix_layer = MHPermutMix(d_model, seq_length, nhead, d_model)
+ *   spectre_vit/models/spectre/spectre.py:66   x = self.norm1(self.mix_layer(x)) + x
+ * i.e. the arithmetic a `mix_layer.forward(x:[B,T,E]) -> [B,T,E]` occupant runs in
+ * forward and in autograd backward.  Plain pointers and sizes only; no torch types.
+ *
+ * Common conventions
+ *   - activations x, y, dy, dx: contiguous [B, T, E] with T = has_cls + H*W, E innermost,
+ *     token 0 = CLS when has_cls=1 (spectre.py:151-152,182,198); CLS is passed through
+ *     (y[:,0] = x[:,0], dx[:,0] = dy[:,0]).
+ *   - act_dtype: 0 = float32, 1 = bfloat16.  All arithmetic is fp32; bf16 is I/O only
+ *     (torch.fft up-casts bf16 under autocast: SURVEY.md section 0.4).
+ *   - learned parameters and their gradients are always float32.
+ *   - every pointer is DEVICE memory on the current CUDA device, 16-byte aligned;
+ *     E must be even.  The caller owns every buffer (outputs and workspace included);
+ *     the library never allocates, frees or synchronises, and only enqueues work on
+ *     `stream` (a cudaStream_t passed as void*; NULL = legacy default stream), so the
+ *     calls are CUDA-graph capturable.
+ *   - return value: 0 on success; negative SPECTRE_E_* otherwise, with a message
+ *     retrievable through spectre_last_error() (thread-local).  There is no CPU
+ *     fallback and no fallback to torch.fft: unsupported grids are an error.
+ */
+#ifndef SPECTRE_B200_H_
+#define SPECTRE_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPECTRE_DTYPE_F32 0
+#define SPECTRE_DTYPE_BF16 1
+
+#define SPECTRE_OK 0
+#define SPECTRE_E_NULL (-1)        /* a required pointer is NULL */
+#define SPECTRE_E_SHAPE (-2)       /* B/E/H/W out of range, E odd, H or W odd for DWT */
+#define SPECTRE_E_GRID (-3)        /* (H, W) has no compiled kernel */
+#define SPECTRE_E_DTYPE (-4)       /* act_dtype not 0/1 */
+#define SPECTRE_E_ALIGN (-5)       /* pointer not 16-byte aligned */
+#define SPECTRE_E_WORKSPACE (-6)   /* workspace_bytes too small */
+#define SPECTRE_E_CUDA (-7)        /* launch failed; message holds cudaGetErrorString */
+
+/* FFT mixer forward  (replaces: rfft2 -> * filter -> irfft2 in the mix_layer slot;
+ * conventions of torch.fft.rfft2(..., norm="ortho") at spectre.py:136 and the
+ * 2-D FFT token mixer at spectre_vit/repl/orthogonal_permut.py:23-28).
+ *   y[:,1:] = irfft2( rfft2(x[:,1:] as [B,H,W,E], dims (1,2), ortho) * filt, s=(H,W), ortho )
+ * filt: float32 [H, W/2+1, E, 2] (re, im interleaved). */
+int spectre_fftmix_fwd(const void* x, const float* filt, void* y,
+                       int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);
+
+/* FFT mixer backward (autograd of the above):
+ *   dx    = irfft2( conj(filt) * rfft2(dy) )
+ *   dfilt = sum_b conj(rfft2(x_b)) * (c * rfft2(dy_b)),  c[kw] = 1 for kw=0 and (W even) kw=W/2, else 2
+ * dfilt: float32 [H, W/2+1, E, 2], fully overwritten (not accumulated).
+ * workspace: >= spectre_fftmix_bwd_workspace_bytes(B,H,W,E) bytes, holds the per-CTA
+ * partial filter gradients that a second tiny kernel sums in a fixed order
+ * (deterministic; no atomics). */
+int spectre_fftmix_bwd(const void* dy, const void* x, const float* filt,
+                       void* dx, float* dfilt, void* workspace, size_t workspace_bytes,
+                       int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);
+size_t spectre_fftmix_bwd_workspace_bytes(int B, int H, int W, int E);
+
+/* Haar DWT mixer forward (single-level orthonormal 2-D Haar over the token grid, even H, W;
+ * convention of DWTForward(wave="haar", mode="zero") at spectre_vit/repl/dwt_experiments.py:9,56;
+ * mode names dwt_token/dwt_embed at spectre.py:33-34):
+ *   y[:,1:] = IDWT( w * DWT(x[:,1:] as [B,H,W,E]) )
+ * w: float32 [4, H/2, W/2, E], sub-band order (LL, W-low/H-high, W-high/H-low, HH). */
+int spectre_dwtmix_fwd(const void* x, const float* w, void* y,
+                       int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);
+
+/* Haar DWT mixer backward (row A6): dx = IDWT(w * DWT(dy)); dw = sum_b DWT(x_b) * DWT(dy_b).
+ * dw: float32 [4, H/2, W/2, E], fully overwritten. */
+int spectre_dwtmix_bwd(const void* dy, const void* x, const float* w,
+                       void* dx, float* dw, void* workspace, size_t workspace_bytes,
+                       int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);
+size_t spectre_dwtmix_bwd_workspace_bytes(int B, int H, int W, int E);
+
+/* 1 if (H, W) has a compiled FFT-mixer kernel, else 0. */
+int spectre_fftmix_supported(int H, int W);
+
+/* Number of kernels the last successful call on this thread enqueued (for launch accounting). */
+int spectre_last_launch_count(void);
+
+/* Thread-local message for the last non-zero return on this thread ("" if none). */
+const char* spectre_last_error(void);
+
+/* "spectre_b200 <version> sm_100a" */
+const char* spectre_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPECTRE_B200_H_ */

@@ -1,0 +1,100 @@
+"""Isolated timing of every mixer kernel at the BASELINE.json shapes (CUDA events, inputs > L2
+or L2 flushed between iterations).  Prints one JSON line per kernel:
+    achieved GB/s = algorithmic bytes (fwd 2*T*E*s*B + F, bwd 3*T*E*s*B + 2F) / time.
+Usage: python profiles/kernel_bench.py [--iters 20] [--only fft|dwt]
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from vit_spectre_experiments_b200 import _lib  # noqa: E402
+
+PEAK = 6552.3
+try:
+    PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:
+    pass
+
+SHAPES = [
+    # name, kind, B, H, W, E, dtype
+    ("C1 8x8 E512 f32 B8", "fft", 8, 8, 8, 512, torch.float32),
+    ("C1-shape 8x8 E512 f32 B1024", "fft", 1024, 8, 8, 512, torch.float32),
+    ("C2 7x7 E48 f32 B4096", "fft", 4096, 7, 7, 48, torch.float32),
+    ("8x8 E512 bf16 B1024", "fft", 1024, 8, 8, 512, torch.bfloat16),
+    ("C3 dwt 8x8 E512 bf16 B1024", "dwt", 1024, 8, 8, 512, torch.bfloat16),
+    ("dwt 8x8 E512 f32 B1024", "dwt", 1024, 8, 8, 512, torch.float32),
+    ("dwt 14x14 E384 bf16 B256", "dwt", 256, 14, 14, 384, torch.bfloat16),
+    ("C4 14x14 E384 bf16 B256", "fft", 256, 14, 14, 384, torch.bfloat16),
+    ("C4-shape 14x14 E384 f32 B256", "fft", 256, 14, 14, 384, torch.float32),
+    ("C5 14x14 E768 bf16 B128", "fft", 128, 14, 14, 768, torch.bfloat16),
+    ("C4x4 14x14 E384 bf16 B1024", "fft", 1024, 14, 14, 384, torch.bfloat16),
+]
+
+
+def time_ms(fn, iters, flush):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        flush.zero_()  # 256 MiB write: evicts the 126 MB L2
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        fn()
+        e.record()
+        torch.cuda.synchronize()
+        ts.append(s.elapsed_time(e))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    st = lambda: torch.cuda.current_stream().cuda_stream
+    for name, kind, B, H, W, E, dt in SHAPES:
+        if args.only and args.only != kind:
+            continue
+        T = H * W + 1
+        s = 4 if dt == torch.float32 else 2
+        code = 0 if dt == torch.float32 else 1
+        x = torch.randn(B, T, E, device=dev).to(dt)
+        dy = torch.randn(B, T, E, device=dev).to(dt)
+        y = torch.empty_like(x)
+        dx = torch.empty_like(x)
+        if kind == "fft":
+            p = torch.randn(H, W // 2 + 1, E, 2, device=dev)
+            nws = lib.spectre_fftmix_bwd_workspace_bytes(B, H, W, E)
+        else:
+            p = torch.randn(4, H // 2, W // 2, E, device=dev)
+            nws = lib.spectre_dwtmix_bwd_workspace_bytes(B, H, W, E)
+        dp = torch.empty_like(p)
+        ws = torch.empty(max(nws, 16), dtype=torch.uint8, device=dev)
+        F = p.numel() * 4
+        if kind == "fft":
+            fwd = lambda: _lib.check(lib.spectre_fftmix_fwd(x.data_ptr(), p.data_ptr(), y.data_ptr(), B, H, W, E, 1, code, st()), "fwd")
+            bwd = lambda: _lib.check(lib.spectre_fftmix_bwd(dy.data_ptr(), x.data_ptr(), p.data_ptr(), dx.data_ptr(), dp.data_ptr(), ws.data_ptr(), nws, B, H, W, E, 1, code, st()), "bwd")
+        else:
+            fwd = lambda: _lib.check(lib.spectre_dwtmix_fwd(x.data_ptr(), p.data_ptr(), y.data_ptr(), B, H, W, E, 1, code, st()), "fwd")
+            bwd = lambda: _lib.check(lib.spectre_dwtmix_bwd(dy.data_ptr(), x.data_ptr(), p.data_ptr(), dx.data_ptr(), dp.data_ptr(), ws.data_ptr(), nws, B, H, W, E, 1, code, st()), "bwd")
+        for which, fn, nbytes in (("fwd", fwd, 2 * B * T * E * s + F), ("bwd", bwd, 3 * B * T * E * s + 2 * F)):
+            med, best = time_ms(fn, args.iters, flush)
+            print(json.dumps({
+                "kernel": f"{kind}mix_{which}", "shape": name, "ms_median": round(med, 4), "ms_best": round(best, 4),
+                "algo_MB": round(nbytes / 1e6, 2), "GBps_median": round(nbytes / med / 1e6, 1),
+                "GBps_best": round(nbytes / best / 1e6, 1), "frac_of_measured_peak": round(nbytes / med / 1e6 / PEAK, 3),
+                "workspace_MB": round(nws / 1e6, 2),
+            }), flush=True)
+
+
+if __name__ == "__main__":
+    main()

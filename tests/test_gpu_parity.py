@@ -1,0 +1,168 @@
+"""Parity of the CUDA mixers (through the C ABI) against the oracle.  `-m gpu` only.
+
+Bar (BASELINE.json north_star): max-abs error relative to the largest reference magnitude
+<= 1e-5 for float32 I/O, <= 3e-2 for bfloat16 I/O (oracle = fp32 torch.fft on the bf16-rounded
+inputs, rounded to bf16).
+"""
+import pytest
+import torch
+
+from oracle import mixers_ref as O
+
+pytestmark = pytest.mark.gpu
+
+TOL = {torch.float32: 1e-5, torch.bfloat16: 3e-2}
+# fp32 parameter gradients computed from bf16 activations are not rounded to bf16 on output
+TOL_PARAM = {torch.float32: 2e-5, torch.bfloat16: 2e-3}
+
+
+def rel_err(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+def make(B, H, W, E, dtype, has_cls, seed, kind):
+    g = torch.Generator().manual_seed(seed)
+    T = H * W + int(has_cls)
+    x = torch.randn(B, T, E, generator=g).to(dtype)
+    dy = torch.randn(B, T, E, generator=g).to(dtype)
+    if kind == "fft":
+        p = torch.randn(H, W // 2 + 1, E, 2, generator=g)     # O(1) complex filter, non-Hermitian
+    else:
+        p = 1.0 + 0.5 * torch.randn(4, H // 2, W // 2, E, generator=g)
+    return x, dy, p
+
+
+FFT_CASES = [
+    # B, H, W, E, dtype                      which BASELINE.json config
+    (8, 8, 8, 512, torch.float32),           # C1 tiny FFT-mix CIFAR-shaped
+    (8, 7, 7, 48, torch.float32),            # C2 tiny FFT-mix MNIST-shaped (E=48: ragged channel tile)
+    (67, 7, 7, 48, torch.float32),           # C2, odd batch (ragged image group)
+    (4, 14, 14, 384, torch.bfloat16),        # C4 ViT-S/16
+    (3, 14, 14, 384, torch.float32),
+    (2, 14, 14, 768, torch.bfloat16),        # C5 ViT-B/16
+    (5, 8, 8, 512, torch.bfloat16),
+    (3, 16, 16, 64, torch.float32),
+    (3, 16, 16, 64, torch.bfloat16),
+    (9, 4, 4, 32, torch.float32),
+    (1, 8, 8, 2, torch.float32),             # single channel pair
+    (300, 14, 14, 64, torch.bfloat16),       # more image groups than CTAs in y
+]
+
+
+@pytest.mark.parametrize("B,H,W,E,dtype", FFT_CASES)
+@pytest.mark.parametrize("has_cls", [True, False])
+def test_fftmix_fwd_bwd(cuda_device, B, H, W, E, dtype, has_cls):
+    from vit_spectre_experiments_b200 import fft_mix
+
+    if not has_cls and B > 9:
+        pytest.skip("has_cls=False covered on the small cases")
+    x, dy, filt = make(B, H, W, E, dtype, has_cls, 1234 + B + E, "fft")
+    xd = x.to(cuda_device).requires_grad_(True)
+    fd = filt.to(cuda_device).requires_grad_(True)
+    y = fft_mix(xd, fd, (H, W), has_cls)
+    assert y.dtype == dtype and y.shape == x.shape
+    y.backward(dy.to(cuda_device))
+
+    xr, dyr = x.float(), dy.float()
+    if not has_cls:  # oracle always carries a CLS row: prepend a dummy one
+        xr = torch.cat([torch.zeros(B, 1, E), xr], 1)
+        dyr = torch.cat([torch.zeros(B, 1, E), dyr], 1)
+    y_ref = O.fft_mix_ref(xr, filt, H, W)
+    dx_ref, df_ref = O.fft_mix_bwd_ref(dyr, xr, filt, H, W)
+    if not has_cls:
+        y_ref, dx_ref = y_ref[:, 1:], dx_ref[:, 1:]
+    y_ref, dx_ref = y_ref.to(dtype), dx_ref.to(dtype)
+
+    assert rel_err(y, y_ref) <= TOL[dtype]
+    assert rel_err(xd.grad, dx_ref) <= TOL[dtype]
+    assert xd.grad.dtype == dtype and fd.grad.dtype == torch.float32
+    assert rel_err(fd.grad, df_ref) <= TOL_PARAM[dtype]
+    if has_cls:  # CLS row is a bit-exact passthrough in both directions
+        assert torch.equal(y[:, 0].cpu(), x[:, 0])
+        assert torch.equal(xd.grad[:, 0].cpu(), dy[:, 0])
+
+
+DWT_CASES = [
+    (32, 8, 8, 512, torch.bfloat16),         # C3 DWT-mix CIFAR-shaped (batch reduced)
+    (8, 8, 8, 512, torch.float32),
+    (3, 14, 14, 384, torch.bfloat16),
+    (3, 14, 14, 384, torch.float32),
+    (5, 4, 6, 16, torch.float32),            # non-square grid
+    (1, 2, 2, 8, torch.bfloat16),
+    (700, 8, 8, 64, torch.bfloat16),         # more images than y-slabs
+]
+
+
+@pytest.mark.parametrize("B,H,W,E,dtype", DWT_CASES)
+@pytest.mark.parametrize("has_cls", [True, False])
+def test_dwtmix_fwd_bwd(cuda_device, B, H, W, E, dtype, has_cls):
+    from vit_spectre_experiments_b200 import dwt_mix
+
+    if not has_cls and B > 9:
+        pytest.skip("has_cls=False covered on the small cases")
+    x, dy, w = make(B, H, W, E, dtype, has_cls, 99 + B + E, "dwt")
+    xd = x.to(cuda_device).requires_grad_(True)
+    wd = w.to(cuda_device).requires_grad_(True)
+    y = dwt_mix(xd, wd, (H, W), has_cls)
+    y.backward(dy.to(cuda_device))
+
+    xr, dyr = x.float(), dy.float()
+    if not has_cls:
+        xr = torch.cat([torch.zeros(B, 1, E), xr], 1)
+        dyr = torch.cat([torch.zeros(B, 1, E), dyr], 1)
+    y_ref = O.dwt_mix_ref(xr, w, H, W)
+    dx_ref, dw_ref = O.dwt_mix_bwd_ref(dyr, xr, w, H, W)
+    if not has_cls:
+        y_ref, dx_ref = y_ref[:, 1:], dx_ref[:, 1:]
+    assert rel_err(y, y_ref.to(dtype)) <= TOL[dtype]
+    assert rel_err(xd.grad, dx_ref.to(dtype)) <= TOL[dtype]
+    assert rel_err(wd.grad, dw_ref) <= TOL_PARAM[dtype]
+    if has_cls:
+        assert torch.equal(y[:, 0].cpu(), x[:, 0])
+
+
+def test_identity_filter_and_linearity_full_size(cuda_device):
+    """Size-independent properties at BASELINE.json's full C4 shape ([256,197,384] bf16):
+    identity filter => y == x (up to bf16 rounding of an exact round trip); linearity in x."""
+    from vit_spectre_experiments_b200 import fft_mix
+
+    B, H, W, E = 256, 14, 14, 384
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(B, 197, E, generator=g).to(torch.bfloat16).to(cuda_device)
+    ident = torch.zeros(H, W // 2 + 1, E, 2, device=cuda_device)
+    ident[..., 0] = 1
+    y = fft_mix(x, ident, (H, W))
+    assert rel_err(y, x) <= 3e-2
+    assert (y.float() - x.float()).abs().max().item() <= 2 ** -6 * x.float().abs().max().item()
+    filt = torch.randn(H, W // 2 + 1, E, 2, generator=g).to(cuda_device)
+    x32 = x.float()
+    a = fft_mix(x32, filt, (H, W))
+    b = fft_mix(2 * x32, filt, (H, W))
+    assert rel_err(b, 2 * a) <= 1e-6
+    # Parseval: ortho transforms with a unit-modulus Hermitian-compatible filter preserve energy
+    assert abs(y.float().pow(2).sum().item() / x.float().pow(2).sum().item() - 1) < 1e-2
+
+
+def test_dwt_perfect_reconstruction_full_size(cuda_device):
+    """C3 full shape [1024,65,512] bf16: unit weights => y == x exactly representable."""
+    from vit_spectre_experiments_b200 import dwt_mix
+
+    x = torch.randn(1024, 65, 512, generator=torch.Generator().manual_seed(3)).to(torch.bfloat16).to(cuda_device)
+    w = torch.ones(4, 4, 4, 512, device=cuda_device)
+    y = dwt_mix(x, w, (8, 8))
+    assert rel_err(y, x) <= 4e-3
+
+
+def test_errors_are_loud(cuda_device):
+    from vit_spectre_experiments_b200 import dwt_mix, fft_mix
+
+    x = torch.randn(2, 26, 8, device=cuda_device)
+    with pytest.raises(RuntimeError, match="no kernel compiled"):
+        fft_mix(x, torch.randn(5, 3, 8, 2, device=cuda_device), (5, 5))
+    with pytest.raises(RuntimeError, match="float32 or bfloat16"):
+        fft_mix(torch.randn(2, 65, 8, device=cuda_device).half(), torch.randn(8, 5, 8, 2, device=cuda_device), (8, 8))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        fft_mix(torch.randn(2, 65, 8), torch.randn(8, 5, 8, 2), (8, 8))
+    with pytest.raises(RuntimeError, match="even"):
+        dwt_mix(torch.randn(2, 50, 8, device=cuda_device), torch.randn(4, 3, 3, 8, device=cuda_device), (7, 7))

@@ -1,0 +1,83 @@
+"""ctypes binding of ``libspectre_b200.so`` (C ABI: ``include/spectre_b200.h``).
+
+There is deliberately no fallback: if the library has not been built, importing the
+kernels raises, and every entry point raises ``RuntimeError`` on a non-zero return code.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libspectre_b200.so")
+
+# every symbol include/spectre_b200.h declares
+EXPORTED_SYMBOLS = (
+    "spectre_fftmix_fwd",
+    "spectre_fftmix_bwd",
+    "spectre_fftmix_bwd_workspace_bytes",
+    "spectre_dwtmix_fwd",
+    "spectre_dwtmix_bwd",
+    "spectre_dwtmix_bwd_workspace_bytes",
+    "spectre_fftmix_supported",
+    "spectre_last_launch_count",
+    "spectre_last_error",
+    "spectre_version",
+)
+
+_lock = threading.Lock()
+_lib = None
+_p, _i, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+
+
+def load() -> ctypes.CDLL:
+    """Load (once) and type the library.  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: the spectral mixer has no CPU / torch.fft fallback. "
+                "Build it with `python -m vit_spectre_experiments_b200.build` (needs nvcc)."
+            )
+        lib = ctypes.CDLL(LIB_PATH)
+        lib.spectre_fftmix_fwd.argtypes = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_fftmix_fwd.restype = _i
+        lib.spectre_fftmix_bwd.argtypes = [_p, _p, _p, _p, _p, _p, _sz, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_fftmix_bwd.restype = _i
+        lib.spectre_fftmix_bwd_workspace_bytes.argtypes = [_i, _i, _i, _i]
+        lib.spectre_fftmix_bwd_workspace_bytes.restype = _sz
+        lib.spectre_dwtmix_fwd.argtypes = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_dwtmix_fwd.restype = _i
+        lib.spectre_dwtmix_bwd.argtypes = [_p, _p, _p, _p, _p, _p, _sz, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_dwtmix_bwd.restype = _i
+        lib.spectre_dwtmix_bwd_workspace_bytes.argtypes = [_i, _i, _i, _i]
+        lib.spectre_dwtmix_bwd_workspace_bytes.restype = _sz
+        lib.spectre_fftmix_supported.argtypes = [_i, _i]
+        lib.spectre_fftmix_supported.restype = _i
+        lib.spectre_last_launch_count.argtypes = []
+        lib.spectre_last_launch_count.restype = _i
+        lib.spectre_last_error.argtypes = []
+        lib.spectre_last_error.restype = ctypes.c_char_p
+        lib.spectre_version.argtypes = []
+        lib.spectre_version.restype = ctypes.c_char_p
+        _lib = lib
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().spectre_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"{what} failed (code {rc}): {msg}")
+
+
+# running count of kernels enqueued through this binding (bench.py reports it)
+launch_counter = {"kernels": 0}
+
+
+def count_launches() -> None:
+    launch_counter["kernels"] += load().spectre_last_launch_count()

@@ -1,0 +1,150 @@
+// extern "C" entry points declared in include/spectre_b200.h: argument validation,
+// error bookkeeping, dispatch to the templated launchers.  No torch types here.
+#include <cstdarg>
+
+#include "common.cuh"
+
+namespace sb200 {
+
+int fftmix_supported(int H, int W);
+int fftmix_fwd_dispatch(const void* x, const float* filt, void* y, int B, int H, int W, int E, int cls, int dtype,
+                        cudaStream_t st);
+int fftmix_bwd_dispatch(const void* dy, const void* x, const float* filt, void* dx, float* dfilt, void* ws,
+                        size_t ws_bytes, int B, int H, int W, int E, int cls, int dtype, cudaStream_t st);
+size_t fftmix_bwd_workspace(int B, int H, int W, int E);
+int dwtmix_dispatch(bool backward, const void* in, const void* xsave, const float* w, void* out, float* dw, void* ws,
+                    size_t ws_bytes, int B, int H, int W, int E, int cls, int dtype, cudaStream_t st);
+size_t dwtmix_bwd_workspace(int B, int H, int W, int E);
+
+std::string& last_error() {
+  thread_local std::string msg;
+  return msg;
+}
+int& last_launch_count() {
+  thread_local int n = 0;
+  return n;
+}
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  last_error() = buf;
+  last_launch_count() = 0;
+  return code;
+}
+int device_sm_count() {
+  thread_local int cached_dev = -1, cached_sms = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev != cached_dev) {
+    cudaDeviceGetAttribute(&cached_sms, cudaDevAttrMultiProcessorCount, dev);
+    cached_dev = dev;
+  }
+  return cached_sms > 0 ? cached_sms : 148;
+}
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const float4* __restrict__ part, float4* __restrict__ out,
+                                                              size_t n4, int slabs) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  float4 s = part[i];
+  for (int k = 1; k < slabs; ++k) {
+    const float4 t = part[static_cast<size_t>(k) * n4 + i];
+    s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+  }
+  out[i] = s;
+}
+
+void launch_reduce_partials(const float* part, float* out, size_t n_floats, int slabs, cudaStream_t stream) {
+  const size_t n4 = n_floats / 4;
+  const unsigned blocks = static_cast<unsigned>((n4 + 255) / 256);
+  reduce_partials_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(part),
+                                                     reinterpret_cast<float4*>(out), n4, slabs);
+}
+
+static int check_common(const char* fn, int B, int H, int W, int E, int has_cls, int dtype) {
+  if (B < 1 || H < 1 || W < 1 || E < 2 || (E & 1) || (has_cls != 0 && has_cls != 1))
+    return fail(SPECTRE_E_SHAPE, "%s: bad shape B=%d H=%d W=%d E=%d has_cls=%d (need B>=1, E even)", fn, B, H, W, E,
+                has_cls);
+  if (dtype != SPECTRE_DTYPE_F32 && dtype != SPECTRE_DTYPE_BF16)
+    return fail(SPECTRE_E_DTYPE, "%s: act_dtype=%d (0=float32, 1=bfloat16)", fn, dtype);
+  return SPECTRE_OK;
+}
+
+}  // namespace sb200
+
+using namespace sb200;
+
+extern "C" {
+
+int spectre_fftmix_fwd(const void* x, const float* filt, void* y, int B, int H, int W, int E, int has_cls, int act_dtype,
+                       void* stream) {
+  if (!x || !filt || !y) return fail(SPECTRE_E_NULL, "spectre_fftmix_fwd: null pointer");
+  if (int rc = check_common("spectre_fftmix_fwd", B, H, W, E, has_cls, act_dtype)) return rc;
+  if (!aligned16(x) || !aligned16(filt) || !aligned16(y))
+    return fail(SPECTRE_E_ALIGN, "spectre_fftmix_fwd: pointers must be 16-byte aligned");
+  if (act_dtype == SPECTRE_DTYPE_BF16 && ((static_cast<long long>(H) * W + has_cls) * E) % 2)
+    return fail(SPECTRE_E_SHAPE, "spectre_fftmix_fwd: odd element count");
+  const int rc = fftmix_fwd_dispatch(x, filt, y, B, H, W, E, has_cls, act_dtype, static_cast<cudaStream_t>(stream));
+  if (rc == SPECTRE_OK) last_error().clear();
+  return rc;
+}
+
+int spectre_fftmix_bwd(const void* dy, const void* x, const float* filt, void* dx, float* dfilt, void* workspace,
+                       size_t workspace_bytes, int B, int H, int W, int E, int has_cls, int act_dtype, void* stream) {
+  if (!dy || !x || !filt || !dx || !dfilt) return fail(SPECTRE_E_NULL, "spectre_fftmix_bwd: null pointer");
+  if (int rc = check_common("spectre_fftmix_bwd", B, H, W, E, has_cls, act_dtype)) return rc;
+  if (!aligned16(dy) || !aligned16(x) || !aligned16(filt) || !aligned16(dx) || !aligned16(dfilt) ||
+      !aligned16(workspace))
+    return fail(SPECTRE_E_ALIGN, "spectre_fftmix_bwd: pointers must be 16-byte aligned");
+  const int rc = fftmix_bwd_dispatch(dy, x, filt, dx, dfilt, workspace, workspace ? workspace_bytes : 0, B, H, W, E,
+                                     has_cls, act_dtype, static_cast<cudaStream_t>(stream));
+  if (rc == SPECTRE_OK) last_error().clear();
+  return rc;
+}
+
+size_t spectre_fftmix_bwd_workspace_bytes(int B, int H, int W, int E) {
+  if (B < 1 || E < 2 || !fftmix_supported(H, W)) return 0;
+  return fftmix_bwd_workspace(B, H, W, E);
+}
+
+int spectre_dwtmix_fwd(const void* x, const float* w, void* y, int B, int H, int W, int E, int has_cls, int act_dtype,
+                       void* stream) {
+  if (!x || !w || !y) return fail(SPECTRE_E_NULL, "spectre_dwtmix_fwd: null pointer");
+  if (int rc = check_common("spectre_dwtmix_fwd", B, H, W, E, has_cls, act_dtype)) return rc;
+  if ((H & 1) || (W & 1)) return fail(SPECTRE_E_SHAPE, "spectre_dwtmix_fwd: Haar needs even H, W (got %dx%d)", H, W);
+  if (!aligned16(x) || !aligned16(w) || !aligned16(y))
+    return fail(SPECTRE_E_ALIGN, "spectre_dwtmix_fwd: pointers must be 16-byte aligned");
+  const int rc = dwtmix_dispatch(false, x, nullptr, w, y, nullptr, nullptr, 0, B, H, W, E, has_cls, act_dtype,
+                                 static_cast<cudaStream_t>(stream));
+  if (rc == SPECTRE_OK) last_error().clear();
+  return rc;
+}
+
+int spectre_dwtmix_bwd(const void* dy, const void* x, const float* w, void* dx, float* dw, void* workspace,
+                       size_t workspace_bytes, int B, int H, int W, int E, int has_cls, int act_dtype, void* stream) {
+  if (!dy || !x || !w || !dx || !dw) return fail(SPECTRE_E_NULL, "spectre_dwtmix_bwd: null pointer");
+  if (int rc = check_common("spectre_dwtmix_bwd", B, H, W, E, has_cls, act_dtype)) return rc;
+  if ((H & 1) || (W & 1)) return fail(SPECTRE_E_SHAPE, "spectre_dwtmix_bwd: Haar needs even H, W (got %dx%d)", H, W);
+  if (!aligned16(dy) || !aligned16(x) || !aligned16(w) || !aligned16(dx) || !aligned16(dw) || !aligned16(workspace))
+    return fail(SPECTRE_E_ALIGN, "spectre_dwtmix_bwd: pointers must be 16-byte aligned");
+  const int rc = dwtmix_dispatch(true, dy, x, w, dx, dw, workspace, workspace ? workspace_bytes : 0, B, H, W, E, has_cls,
+                                 act_dtype, static_cast<cudaStream_t>(stream));
+  if (rc == SPECTRE_OK) last_error().clear();
+  return rc;
+}
+
+size_t spectre_dwtmix_bwd_workspace_bytes(int B, int H, int W, int E) {
+  if (B < 1 || E < 2 || H < 2 || W < 2 || (H & 1) || (W & 1)) return 0;
+  return dwtmix_bwd_workspace(B, H, W, E);
+}
+
+int spectre_fftmix_supported(int H, int W) { return fftmix_supported(H, W); }
+int spectre_last_launch_count(void) { return last_launch_count(); }
+const char* spectre_last_error(void) { return last_error().c_str(); }
+const char* spectre_version(void) { return "spectre_b200 0.1.0 sm_100a"; }
+
+}  // extern "C"

@@ -1,0 +1,90 @@
+// Shared helpers for the mixer kernels: streaming global I/O of channel pairs /
+// channel vectors, the deterministic partial-sum reduction, launch bookkeeping.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "../../include/spectre_b200.h"
+
+namespace sb200 {
+
+// ------------------------------------------------------------------ error / launch bookkeeping
+std::string& last_error();
+int& last_launch_count();
+int fail(int code, const char* fmt, ...);
+int device_sm_count();
+bool aligned16(const void* p);
+
+// ------------------------------------------------------------------ channel-pair I/O
+// One thread moves two adjacent channels: a 64-bit access for fp32, a 32-bit
+// access for bf16.  Activations are touched exactly once, so loads/stores use the
+// streaming (evict-first) cache policy and leave L2 to the filter / partials.
+template <class T>
+struct PairIO;
+
+template <>
+struct PairIO<float> {
+  static __device__ __forceinline__ float2 ld(const float* p) { return __ldcs(reinterpret_cast<const float2*>(p)); }
+  static __device__ __forceinline__ void st(float* p, float2 v) { __stcs(reinterpret_cast<float2*>(p), v); }
+};
+
+template <>
+struct PairIO<__nv_bfloat16> {
+  static __device__ __forceinline__ float2 ld(const __nv_bfloat16* p) {
+    const unsigned u = __ldcs(reinterpret_cast<const unsigned*>(p));
+    return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
+  }
+  static __device__ __forceinline__ void st(__nv_bfloat16* p, float2 v) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+    __stcs(reinterpret_cast<unsigned*>(p), *reinterpret_cast<const unsigned*>(&h));
+  }
+};
+
+// ------------------------------------------------------------------ 16-byte channel-vector I/O (DWT kernels)
+template <class T>
+struct VecIO;
+
+template <>
+struct VecIO<float> {
+  static constexpr int kLanes = 4;
+  static __device__ __forceinline__ void ld(const float* p, float (&v)[4]) {
+    const float4 q = __ldcs(reinterpret_cast<const float4*>(p));
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+  }
+  static __device__ __forceinline__ void st(float* p, const float (&v)[4]) {
+    __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3]));
+  }
+};
+
+template <>
+struct VecIO<__nv_bfloat16> {
+  static constexpr int kLanes = 8;
+  static __device__ __forceinline__ void ld(const __nv_bfloat16* p, float (&v)[8]) {
+    const uint4 q = __ldcs(reinterpret_cast<const uint4*>(p));
+    const unsigned u[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(u[i] << 16);
+      v[2 * i + 1] = __uint_as_float(u[i] & 0xffff0000u);
+    }
+  }
+  static __device__ __forceinline__ void st(__nv_bfloat16* p, const float (&v)[8]) {
+    unsigned u[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+      u[i] = *reinterpret_cast<const unsigned*>(&h);
+    }
+    __stcs(reinterpret_cast<uint4*>(p), make_uint4(u[0], u[1], u[2], u[3]));
+  }
+};
+
+// out[i] = sum_{s<slabs} part[s*n4 + i]  (float4 granularity, fixed order => deterministic)
+void launch_reduce_partials(const float* part, float* out, size_t n_floats, int slabs, cudaStream_t stream);
+
+}  // namespace sb200

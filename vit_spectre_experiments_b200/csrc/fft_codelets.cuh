@@ -29,6 +29,14 @@
 #define SB_HD inline
 #endif
 
+// 1: issue pair arithmetic as packed FADD2/FMUL2/FFMA2; 0: two scalar ops.
+// Measured on B200 (profiles/r01_pipes.txt): scalar FFMA sustains 4.0 warp-instr/clk/SM,
+// FFMA2 1.58 (= 3.2 scalar-equivalent), FADD2 1.6, FMUL2 1.97 -- packed math halves
+// issue slots but not FP-pipe time, so it only pays where issue is the limiter.
+#ifndef SB200_PACKED_MATH
+#define SB200_PACKED_MATH 0
+#endif
+
 namespace sb200 {
 
 // ----------------------------------------------------------------- constexpr trig
@@ -96,7 +104,7 @@ struct VOps<float> {
 template <>
 struct VOps<float2> {
   static SB_HD float2 zero() { return make_float2(0.f, 0.f); }
-#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ >= 1000)
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ >= 1000) && SB200_PACKED_MATH
   static SB_HD float2 add(float2 a, float2 b) { return __fadd2_rn(a, b); }
   static SB_HD float2 sub(float2 a, float2 b) { return __ffma2_rn(b, make_float2(-1.f, -1.f), a); }
   static SB_HD float2 muls(float2 a, float s) { return __fmul2_rn(a, make_float2(s, s)); }

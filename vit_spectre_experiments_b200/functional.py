@@ -1,0 +1,144 @@
+"""Autograd functions over the C-ABI kernels (``include/spectre_b200.h``).
+
+Forward and backward of the occupant of the reference's ``mix_layer`` slot
+(``spectre_vit/models/spectre/spectre.py:50,66``).  torch is plumbing only here: it owns the
+device buffers and the current stream; the arithmetic happens in ``libspectre_b200.so``.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+_DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1}
+
+
+def _act_code(t: torch.Tensor, what: str) -> int:
+    if not t.is_cuda:
+        raise RuntimeError(
+            f"{what}: tensor is on {t.device}; the spectral mixers are CUDA (sm_100a) only and have no CPU fallback"
+        )
+    try:
+        return _DTYPE_CODE[t.dtype]
+    except KeyError:
+        raise RuntimeError(f"{what}: activations must be float32 or bfloat16, got {t.dtype}") from None
+
+
+def _stream_ptr(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _check_tokens(x: torch.Tensor, H: int, W: int, has_cls: bool, what: str) -> None:
+    if x.dim() != 3 or x.shape[1] != H * W + int(has_cls):
+        raise RuntimeError(
+            f"{what}: expected x of shape [B, {H * W + int(has_cls)}, E] for a {H}x{W} grid"
+            f"{' + CLS' if has_cls else ''}, got {tuple(x.shape)}"
+        )
+
+
+class _FFTMix(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, filt, H, W, has_cls):
+        lib = _lib.load()
+        _check_tokens(x, H, W, has_cls, "fft_mix")
+        code = _act_code(x, "fft_mix")
+        if filt.dtype != torch.float32 or tuple(filt.shape) != (H, W // 2 + 1, x.shape[2], 2):
+            raise RuntimeError(
+                f"fft_mix: filter must be float32 [{H}, {W // 2 + 1}, {x.shape[2]}, 2], got {filt.dtype} {tuple(filt.shape)}"
+            )
+        x = x.contiguous()
+        filt = filt.contiguous()
+        y = torch.empty_like(x)
+        B, _, E = x.shape
+        with torch.cuda.device(x.device):
+            rc = lib.spectre_fftmix_fwd(x.data_ptr(), filt.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls), code,
+                                        _stream_ptr(x.device))
+        _lib.check(rc, "spectre_fftmix_fwd")
+        _lib.count_launches()
+        ctx.save_for_backward(x, filt)
+        ctx.grid = (H, W, has_cls)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _lib.load()
+        x, filt = ctx.saved_tensors
+        H, W, has_cls = ctx.grid
+        B, _, E = x.shape
+        dy = dy.contiguous()
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dx = torch.empty_like(x)
+        dfilt = torch.empty_like(filt)
+        with torch.cuda.device(x.device):
+            nbytes = lib.spectre_fftmix_bwd_workspace_bytes(B, H, W, E)
+            ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
+            rc = lib.spectre_fftmix_bwd(dy.data_ptr(), x.data_ptr(), filt.data_ptr(), dx.data_ptr(), dfilt.data_ptr(),
+                                        ws.data_ptr(), nbytes, B, H, W, E, int(has_cls), _act_code(x, "fft_mix"),
+                                        _stream_ptr(x.device))
+        _lib.check(rc, "spectre_fftmix_bwd")
+        _lib.count_launches()
+        return dx, dfilt, None, None, None
+
+
+class _DWTMix(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, H, W, has_cls):
+        lib = _lib.load()
+        _check_tokens(x, H, W, has_cls, "dwt_mix")
+        code = _act_code(x, "dwt_mix")
+        if weight.dtype != torch.float32 or tuple(weight.shape) != (4, H // 2, W // 2, x.shape[2]):
+            raise RuntimeError(
+                f"dwt_mix: weight must be float32 [4, {H // 2}, {W // 2}, {x.shape[2]}], got {weight.dtype} {tuple(weight.shape)}"
+            )
+        x = x.contiguous()
+        weight = weight.contiguous()
+        y = torch.empty_like(x)
+        B, _, E = x.shape
+        with torch.cuda.device(x.device):
+            rc = lib.spectre_dwtmix_fwd(x.data_ptr(), weight.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls), code,
+                                        _stream_ptr(x.device))
+        _lib.check(rc, "spectre_dwtmix_fwd")
+        _lib.count_launches()
+        ctx.save_for_backward(x, weight)
+        ctx.grid = (H, W, has_cls)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _lib.load()
+        x, weight = ctx.saved_tensors
+        H, W, has_cls = ctx.grid
+        B, _, E = x.shape
+        dy = dy.contiguous()
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dx = torch.empty_like(x)
+        dw = torch.empty_like(weight)
+        with torch.cuda.device(x.device):
+            nbytes = lib.spectre_dwtmix_bwd_workspace_bytes(B, H, W, E)
+            ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
+            rc = lib.spectre_dwtmix_bwd(dy.data_ptr(), x.data_ptr(), weight.data_ptr(), dx.data_ptr(), dw.data_ptr(),
+                                        ws.data_ptr(), nbytes, B, H, W, E, int(has_cls), _act_code(x, "dwt_mix"),
+                                        _stream_ptr(x.device))
+        _lib.check(rc, "spectre_dwtmix_bwd")
+        _lib.count_launches()
+        return dx, dw, None, None, None
+
+
+def fft_mix(x: torch.Tensor, filt: torch.Tensor, grid, has_cls: bool = True) -> torch.Tensor:
+    """``cat(cls, irfft2(rfft2(x_grid, ortho) * filt, ortho))`` in one fused CUDA pass.
+
+    x ``[B, has_cls + H*W, E]`` (float32 or bfloat16, CUDA); filt float32 ``[H, W//2+1, E, 2]``.
+    """
+    H, W = grid
+    return _FFTMix.apply(x, filt, int(H), int(W), bool(has_cls))
+
+
+def dwt_mix(x: torch.Tensor, weight: torch.Tensor, grid, has_cls: bool = True) -> torch.Tensor:
+    """``cat(cls, IDWT_haar(weight * DWT_haar(x_grid)))`` in one fused CUDA pass.
+
+    weight float32 ``[4, H/2, W/2, E]`` ordered (LL, W-low/H-high, W-high/H-low, HH).
+    """
+    H, W = grid
+    return _DWTMix.apply(x, weight, int(H), int(W), bool(has_cls))

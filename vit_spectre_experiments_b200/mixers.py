@@ -1,0 +1,115 @@
+"""``nn.Module`` occupants of the reference's ``mix_layer`` slot backed by the CUDA kernels.
+
+Contract (kept from ``MHPermutMix``, ``spectre_vit/models/spectre/layers.py:53-73``): constructed
+positionally as ``(embed_dim, token_dim, num_heads, out_channels)`` by
+``SpectreEncoderLayer.__init__`` (``spectre.py:50``), called as ``forward(x:[B, token_dim, embed_dim])
+-> [B, token_dim, out_channels]`` (``spectre.py:66``), deep-copied by ``_get_clones``
+(``spectre.py:86``), moved with ``.to()``, and serialised through ``state_dict()`` -- so the module
+holds only Parameters and plain ints.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn as nn
+
+from .functional import dwt_mix, fft_mix
+
+
+def _resolve_grid(token_dim: int, grid, has_cls: bool):
+    n = token_dim - int(has_cls)
+    if grid is None:
+        s = math.isqrt(n)
+        grid = (s, s)
+    H, W = int(grid[0]), int(grid[1])
+    if H * W != n:
+        raise ValueError(f"grid {H}x{W} does not cover token_dim={token_dim} (has_cls={has_cls})")
+    return H, W
+
+
+class _Fp32ParamMixin:
+    """Learned spectral parameters stay float32 under ``.half()`` / ``.bfloat16()`` / ``.to(dtype)``:
+    the kernels take fp32 parameters and emit fp32 parameter gradients whatever the activation dtype."""
+
+    _fp32_param = ""
+
+    def _apply(self, fn, recurse=True):
+        super()._apply(fn, recurse)
+        p = getattr(self, self._fp32_param)
+        if p.dtype != torch.float32:
+            p.data = p.data.float()
+            if p.grad is not None:
+                p.grad.data = p.grad.data.float()
+        return self
+
+    @staticmethod
+    def _activation(x: torch.Tensor) -> torch.Tensor:
+        if torch.is_autocast_enabled():
+            dt = torch.get_autocast_dtype("cuda")
+            if dt != torch.bfloat16:
+                raise RuntimeError(f"spectral mixers support autocast to bfloat16 only (got {dt})")
+            if x.dtype != dt:
+                x = x.to(dt)
+        return x
+
+
+class SpectralFilterMix(_Fp32ParamMixin, nn.Module):
+    """rfft2 over the patch grid -> learned complex filter -> irfft2, CLS passed through.
+
+    Parameter ``filter``: float32 ``[H, W//2+1, E, 2]`` (viewed complex).  ``num_heads`` is accepted
+    for signature compatibility and unused.
+    """
+
+    _fp32_param = "filter"
+
+    def __init__(self, embed_dim: int, token_dim: int, num_heads: int, out_channels: int, *, grid=None,
+                 has_cls: bool = True, norm: str = "ortho", init_std: float = 0.02):
+        super().__init__()
+        if out_channels != embed_dim:
+            raise ValueError("SpectralFilterMix keeps the channel count: out_channels must equal embed_dim")
+        if norm != "ortho":
+            raise ValueError('only norm="ortho" (the reference convention, spectre.py:136) is implemented')
+        self.embed_dim, self.token_dim, self.num_heads = embed_dim, token_dim, num_heads
+        self.has_cls = bool(has_cls)
+        self.grid = _resolve_grid(token_dim, grid, self.has_cls)
+        H, W = self.grid
+        f = torch.zeros(H, W // 2 + 1, embed_dim, 2)
+        f[..., 0] = 1.0
+        self.filter = nn.Parameter(f + init_std * torch.randn_like(f))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return fft_mix(self._activation(x), self.filter, self.grid, self.has_cls)
+
+    def extra_repr(self) -> str:
+        return f"embed_dim={self.embed_dim}, grid={self.grid}, has_cls={self.has_cls}"
+
+
+class HaarDWTMix(_Fp32ParamMixin, nn.Module):
+    """Single-level 2-D Haar DWT over the patch grid -> learned real sub-band weights -> IDWT.
+
+    Parameter ``weight``: float32 ``[4, H/2, W/2, E]`` ordered (LL, W-low/H-high, W-high/H-low, HH).
+    """
+
+    _fp32_param = "weight"
+
+    def __init__(self, embed_dim: int, token_dim: int, num_heads: int, out_channels: int, *, grid=None,
+                 has_cls: bool = True, levels: int = 1, init_std: float = 0.02):
+        super().__init__()
+        if out_channels != embed_dim:
+            raise ValueError("HaarDWTMix keeps the channel count: out_channels must equal embed_dim")
+        if levels != 1:
+            raise NotImplementedError("only a single decomposition level is implemented")
+        self.embed_dim, self.token_dim, self.num_heads = embed_dim, token_dim, num_heads
+        self.has_cls = bool(has_cls)
+        self.grid = _resolve_grid(token_dim, grid, self.has_cls)
+        H, W = self.grid
+        if H % 2 or W % 2:
+            raise ValueError(f"Haar DWT needs an even grid, got {H}x{W}")
+        self.weight = nn.Parameter(1.0 + init_std * torch.randn(4, H // 2, W // 2, embed_dim))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return dwt_mix(self._activation(x), self.weight, self.grid, self.has_cls)
+
+    def extra_repr(self) -> str:
+        return f"embed_dim={self.embed_dim}, grid={self.grid}, has_cls={self.has_cls}"

@@ -1,0 +1,176 @@
+"""Host-side mirror of the reference's model classes around the ``mix_layer`` slot.
+
+Same constructor arguments, attribute names and ``state_dict`` keys as the reference, so its
+configs / checkpoints / training scripts keep working; the only change is a ``mixer=`` switch at
+the single line that builds ``mix_layer``:
+
+    reference                                                     here
+    ``SpectreLinear``       models/spectre/layers.py:76-101        :class:`SpectreLinear`
+    ``MHPermutMix``         models/spectre/layers.py:53-73         :class:`MHPermutMix`     (mixer="permut")
+    ``SpectreEncoderLayer`` models/spectre/spectre.py:29-73        :class:`SpectreEncoderLayer`
+    ``SpectreEncoder``      models/spectre/spectre.py:76-103       :class:`SpectreEncoder`
+    ``SpectralPatchEmbed``  models/spectre/spectre.py:106-156      :class:`SpectralPatchEmbed`
+    ``SpectreViT``          models/spectre/spectre.py:159-202      :class:`SpectreViT`
+
+These are ordinary torch modules (GEMMs, LayerNorm, GELU stay library calls: SURVEY.md section 8f marks
+them "next"); the hand-written kernels sit behind ``mix_layer`` only.
+"""
+from __future__ import annotations
+
+import copy
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .mixers import HaarDWTMix, SpectralFilterMix
+
+MIXERS = ("permut", "fft", "dwt")
+
+
+class SpectreLinear(nn.Module):
+    """``GELU(LayerNorm(Linear(x))) + skip(x)``; skip is identity when the widths match and an
+    adaptive average pool over the channel axis otherwise (layers.py:76-101)."""
+
+    def __init__(self, in_channels: int, out_channels: int, tokens=None):
+        super().__init__()
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.sparsity = 1
+        self.register_buffer("local_idx", torch.arange(0, in_channels, self.sparsity))
+        self.local_head = nn.Sequential(
+            nn.Linear(len(self.local_idx), out_channels), nn.LayerNorm(out_channels), nn.GELU()
+        )
+        self.avg_pool = nn.Identity() if in_channels == out_channels else nn.AdaptiveAvgPool1d(out_channels)
+
+    def forward(self, x: torch.Tensor, dim=-1) -> torch.Tensor:
+        return self.local_head(x) + self.avg_pool(x)
+
+
+class MHPermutMix(nn.Module):
+    """The reference's HEAD occupant of the slot (layers.py:53-73): per head a fixed random
+    sign flip + permutation of the flattened ``[T*E]`` vector, heads concatenated on the channel
+    axis, then ``SpectreLinear(E*heads -> out)``.  Kept so reference configs without a ``mixer``
+    key behave as before."""
+
+    def __init__(self, embed_dim: int, token_dim: int, num_heads: int, out_channels: int):
+        super().__init__()
+        flat = embed_dim * token_dim
+        self.num_heads, self.token_dim, self.embed_dim = num_heads, token_dim, embed_dim
+        self.concat_dim = embed_dim * num_heads
+        signs = torch.randint(0, 2, (num_heads, flat), dtype=torch.float32) * 2 - 1
+        self.register_buffer("signs", signs.unsqueeze(0))
+        self.register_buffer("perms", torch.stack([torch.randperm(flat) for _ in range(num_heads)]))
+        self.linear = SpectreLinear(self.concat_dim, out_channels)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        batch = x.shape[0]
+        mixed = x.reshape(batch, -1)[:, self.perms] * self.signs
+        return self.linear(mixed.view(batch, self.token_dim, self.concat_dim))
+
+
+def build_mixer(mixer: str, d_model: int, seq_length: int, nhead: int, grid=None) -> nn.Module:
+    """The one line the build changes: what ``SpectreEncoderLayer`` puts in ``mix_layer``
+    (reference: ``MHPermutMix(d_model, seq_length, nhead, d_model)``, spectre.py:50)."""
+    if mixer == "permut":
+        return MHPermutMix(d_model, seq_length, nhead, d_model)
+    if mixer == "fft":
+        return SpectralFilterMix(d_model, seq_length, nhead, d_model, grid=grid)
+    if mixer == "dwt":
+        return HaarDWTMix(d_model, seq_length, nhead, d_model, grid=grid)
+    raise ValueError(f"unknown mixer {mixer!r}; choose from {MIXERS}")
+
+
+class SpectreEncoderLayer(nn.Module):
+    """``x = LN1(mix(x)) + x ; x = LN2(x + FF(x))`` (spectre.py:65-73)."""
+
+    def __init__(self, seq_length, d_model, nhead, dim_feedforward, dropout, activation, *, mixer="permut",
+                 grid=None):
+        super().__init__()
+        self.mix_layer = build_mixer(mixer, d_model, seq_length, nhead, grid)
+        self.linear1 = SpectreLinear(d_model, dim_feedforward)
+        self.linear3 = SpectreLinear(dim_feedforward, d_model)
+        self.norm1 = nn.LayerNorm(d_model, eps=1e-5)
+        self.norm2 = nn.LayerNorm(d_model, eps=1e-5)
+        self.dropout1 = nn.Dropout(dropout)
+        self.dropout2 = nn.Dropout(dropout)
+        self.activation = getattr(F, activation) if isinstance(activation, str) else activation
+
+    def _ff_block(self, x: torch.Tensor) -> torch.Tensor:
+        return self.dropout2(self.linear3(self.dropout1(self.linear1(x))))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = self.norm1(self.mix_layer(x)) + x
+        return self.norm2(x + self._ff_block(x))
+
+
+class SpectreEncoder(nn.Module):
+    """``num_layers`` deep copies of one layer (identical initial parameters, as the reference's
+    ``_get_clones``, spectre.py:86) and an outer residual ``output + src`` (spectre.py:103)."""
+
+    def __init__(self, encoder_layer: nn.Module, num_layers: int, norm=None):
+        super().__init__()
+        self.layers = nn.ModuleList(copy.deepcopy(encoder_layer) for _ in range(num_layers))
+        self.num_layers = num_layers
+        self.norm = norm
+
+    def forward(self, src: torch.Tensor) -> torch.Tensor:
+        out = src
+        for layer in self.layers:
+            out = layer(out)
+        if self.norm is not None:
+            out = self.norm(out)
+        return out + src
+
+
+class SpectralPatchEmbed(nn.Module):
+    """Non-overlapping PxP patches -> ``Re(rfft2(patch, norm="ortho"))`` -> learnable per-frequency
+    gains -> Linear -> prepend CLS, add positional embeddings, dropout (spectre.py:106-156)."""
+
+    def __init__(self, embed_dim, patch_size, num_patches, dropout, in_channels):
+        super().__init__()
+        self.P = patch_size
+        self.embed_dim = embed_dim
+        half = patch_size // 2 + 1
+        self.freq_weight_h = nn.Parameter(torch.ones(patch_size))
+        self.freq_weight_w = nn.Parameter(torch.ones(half))
+        self.proj = nn.Linear(in_channels * patch_size * half, embed_dim)
+        self.cls_token = nn.Parameter(torch.randn(1, 1, embed_dim))
+        self.position_embeddings = nn.Parameter(torch.randn(1, num_patches + 1, embed_dim))
+        self.dropout = nn.Dropout(dropout)
+
+    def forward(self, img: torch.Tensor) -> torch.Tensor:
+        batch, chans = img.shape[:2]
+        P = self.P
+        patches = img.unfold(2, P, P).unfold(3, P, P)                       # [B, C, nH, nW, P, P]
+        n = patches.size(2) * patches.size(3)
+        patches = patches.contiguous().view(batch, chans, n, P, P)
+        spec = torch.fft.rfft2(patches.float(), norm="ortho").real          # [B, C, N, P, P//2+1]
+        spec = spec * self.freq_weight_h.view(1, 1, 1, P, 1) * self.freq_weight_w.view(1, 1, 1, 1, -1)
+        tokens = self.proj(spec.permute(0, 2, 1, 3, 4).flatten(2))          # [B, N, E]
+        tokens = torch.cat((self.cls_token.expand(batch, -1, -1), tokens), dim=1)
+        return self.dropout(tokens + self.position_embeddings)
+
+
+class SpectreViT(nn.Module):
+    """embed -> encoder -> ``mlp_head(x[:, 0])``; ``return_features=True`` also returns the CLS
+    token (spectre.py:159-202).  ``mixer`` selects the ``mix_layer`` occupant."""
+
+    def __init__(self, img_size=32, patch_size=4, in_channels=3, num_classes=10, embed_dim=768, num_encoders=12,
+                 num_heads=12, hidden_dim=3072, dropout=0.1, activation="gelu", *, mixer="permut"):
+        super().__init__()
+        side = img_size // patch_size
+        num_patches = side * side
+        self.mixer = mixer
+        self.embeddings_block = SpectralPatchEmbed(embed_dim, patch_size, num_patches, dropout, in_channels)
+        layer = SpectreEncoderLayer(
+            seq_length=num_patches + 1, d_model=embed_dim, nhead=num_heads, dim_feedforward=hidden_dim,
+            dropout=dropout, activation=activation, mixer=mixer, grid=(side, side),
+        )
+        self.encoder_blocks = SpectreEncoder(layer, num_layers=num_encoders)
+        self.mlp_head = nn.Sequential(SpectreLinear(embed_dim, num_classes))
+
+    def forward(self, x: torch.Tensor, return_features: bool = False):
+        x = self.encoder_blocks(self.embeddings_block(x))
+        cls_token = x[:, 0, :]
+        logits = self.mlp_head(cls_token)
+        return (logits, cls_token) if return_features else logits
