@@ -166,3 +166,59 @@ def test_errors_are_loud(cuda_device):
         fft_mix(torch.randn(2, 65, 8), torch.randn(8, 5, 8, 2), (8, 8))
     with pytest.raises(RuntimeError, match="even"):
         dwt_mix(torch.randn(2, 50, 8, device=cuda_device), torch.randn(4, 3, 3, 8, device=cuda_device), (7, 7))
+
+
+@pytest.mark.parametrize("name,img_size", [("fft", 28), ("dwt", 32)])
+def test_model_matches_reference_classes_golden(cuda_device, name, img_size):
+    """Whole model: tests/golden/ref_vit_<name>mix.npz was produced by the REFERENCE's SpectreViT with the
+    torch.fft / Haar composition in its mix_layer slot (oracle/make_golden.py).  The mirror with the CUDA
+    mixer in the slot must give the same logits, features and mixer-parameter gradients."""
+    import os
+
+    import numpy as np
+
+    from vit_spectre_experiments_b200 import SpectreViT
+
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", f"ref_vit_{name}mix.npz"))
+    m = SpectreViT(img_size=img_size, patch_size=4, in_channels=3, num_classes=10, embed_dim=16, num_encoders=2,
+                   num_heads=2, hidden_dim=24, dropout=0.0, mixer=name).eval()
+    m.load_state_dict({k[4:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("sd::")}, strict=True)
+    m.to(cuda_device)
+    logits, feat = m(torch.from_numpy(g["img"]).to(cuda_device), return_features=True)
+    loss = logits.square().mean()
+    loss.backward()
+    assert rel_err(logits, torch.from_numpy(g["logits"])) <= 2e-5
+    assert rel_err(feat, torch.from_numpy(g["feat"])) <= 2e-5
+    assert abs(loss.item() - float(g["loss"])) <= 2e-5 * abs(float(g["loss"]))
+    params = dict(m.named_parameters())
+    checked = 0
+    for k in g.files:
+        if k.startswith("grad::"):
+            assert rel_err(params[k[6:]].grad, torch.from_numpy(g[k])) <= 5e-5, k
+            checked += 1
+    assert checked == 2
+
+
+def test_autocast_bf16_and_training_step(cuda_device):
+    """Under torch.autocast(bf16) (the reference trains under autocast, repl/train.py:219) the mixer runs its
+    bf16 kernels, keeps an fp32 filter/gradient, and a few AdamW steps reduce the loss."""
+    from types import SimpleNamespace
+
+    from vit_spectre_experiments_b200.functional import TIMER
+    from vit_spectre_experiments_b200.train import Trainer
+
+    cfg = SimpleNamespace(img_size=32, patch_size=4, in_channels=3, num_classes=10, embed_dim=64, num_encoders=2,
+                          num_heads=4, hidden_dim=96, dropout=0.0, activation="gelu", mixer="fft", precision="bf16",
+                          random_seed=42, learning_rate=1e-3, adam_betas=(0.9, 0.999), adam_weight_decay=0.01)
+    tr = Trainer(cfg, cuda_device)
+    img, lab = tr.synthetic_batch(32)
+    TIMER.reset()
+    TIMER.enabled = True
+    losses = [tr.step(img, lab).item() for _ in range(12)]
+    TIMER.enabled = False
+    summ = TIMER.summary()
+    assert summ["fftmix_fwd"][0] == 24 and summ["fftmix_bwd"][0] == 24
+    assert summ["fftmix_bwd"][2][-1] == 2            # activations were bf16 (2 bytes) inside the kernel
+    f = tr.model.encoder_blocks.layers[0].mix_layer.filter
+    assert f.dtype == torch.float32 and f.grad.dtype == torch.float32
+    assert losses[-1] < losses[0]

@@ -1,0 +1,140 @@
+"""CPU tests of the host side: codelet arithmetic (host build of the device header), the C-ABI
+library's exported symbols, the model-class mirror against reference-generated golden vectors,
+module contract (state_dict, deepcopy, dtype policy), loud failure without a GPU."""
+import copy
+import ctypes
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+PKG = os.path.join(ROOT, "vit_spectre_experiments_b200")
+
+
+@pytest.fixture(scope="module")
+def codelets(tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("codelets") / "libcodelets.so")
+    subprocess.run(["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-I", os.path.join(PKG, "csrc"), "-o", so,
+                    os.path.join(ROOT, "tests", "host_codelets.cpp")], check=True)
+    return ctypes.CDLL(so)
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 5, 6, 7, 8, 9, 10, 12, 14, 16])
+def test_codelets_match_numpy(codelets, n):
+    rng = np.random.default_rng(n)
+    z = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+    for d in (-1, 1):
+        re, im = z.real.copy(), z.imag.copy()
+        assert codelets.codelet_cfft(n, d, _p(re), _p(im)) == 0
+        ref = np.fft.fft(z.astype(np.complex128)) if d < 0 else np.fft.ifft(z.astype(np.complex128)) * n
+        assert np.abs(re + 1j * im - ref).max() / np.abs(ref).max() < 5e-7
+    x = rng.standard_normal(n).astype(np.float32)
+    re, im = np.zeros(n // 2 + 1, np.float32), np.zeros(n // 2 + 1, np.float32)
+    codelets.codelet_rfft(n, _p(x), _p(re), _p(im))
+    ref = np.fft.rfft(x.astype(np.float64))
+    assert np.abs(re + 1j * im - ref).max() / np.abs(ref).max() < 5e-7
+    # C2R on a NON-Hermitian half spectrum: imag of DC / Nyquist must be ignored like torch.fft.irfft
+    Z = rng.standard_normal(n // 2 + 1) + 1j * rng.standard_normal(n // 2 + 1)
+    re, im = Z.real.astype(np.float32), Z.imag.astype(np.float32)
+    out = np.zeros(n, np.float32)
+    codelets.codelet_irfft(n, _p(re), _p(im), _p(out))
+    ref = torch.fft.irfft(torch.tensor(re.astype(np.float64) + 1j * im.astype(np.float64)), n=n, norm="forward").numpy()
+    assert np.abs(out - ref).max() / np.abs(ref).max() < 5e-7
+
+
+def test_library_exports_every_declared_symbol():
+    from vit_spectre_experiments_b200 import _lib
+
+    lib = _lib.load()
+    header = open(os.path.join(ROOT, "include", "spectre_b200.h")).read()
+    declared = set(re.findall(r"\b(spectre_[a-z_0-9]+)\s*\(", header))
+    assert declared == set(_lib.EXPORTED_SYMBOLS)
+    for sym in declared:
+        assert hasattr(lib, sym), sym
+    assert b"sm_100a" in lib.spectre_version()
+    assert lib.spectre_fftmix_supported(14, 14) == 1 and lib.spectre_fftmix_supported(7, 7) == 1
+    assert lib.spectre_fftmix_supported(8, 8) == 1 and lib.spectre_fftmix_supported(5, 9) == 0
+    # argument validation happens before any CUDA call, so it is testable without a GPU
+    assert lib.spectre_fftmix_fwd(None, None, None, 1, 8, 8, 8, 1, 0, None) == -1
+    assert b"null" in lib.spectre_last_error()
+    buf = ctypes.create_string_buffer(64)
+    p = ctypes.addressof(buf)
+    p += (-p) % 16
+    assert lib.spectre_fftmix_fwd(p, p, p, 1, 8, 8, 7, 1, 0, None) == -2      # odd E
+    assert lib.spectre_fftmix_fwd(p, p, p, 1, 8, 8, 8, 1, 5, None) == -4      # dtype
+    assert lib.spectre_fftmix_fwd(p + 4, p, p, 1, 8, 8, 8, 1, 0, None) == -5  # alignment
+    assert lib.spectre_dwtmix_fwd(p, p, p, 1, 7, 7, 8, 1, 0, None) == -2      # odd grid for Haar
+
+
+def test_model_mirror_matches_reference_golden():
+    """SpectreViT mirror + reference state_dict (HEAD MHPermutMix occupant) => reference logits."""
+    from vit_spectre_experiments_b200 import SpectreViT
+
+    g = np.load(os.path.join(GOLD, "ref_vit_permut.npz"))
+    m = SpectreViT(img_size=28, patch_size=4, in_channels=3, num_classes=10, embed_dim=16, num_encoders=2,
+                   num_heads=2, hidden_dim=24, dropout=0.0, mixer="permut").eval()
+    sd = {k[4:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("sd::")}
+    assert set(sd) == set(m.state_dict())
+    m.load_state_dict(sd, strict=True)
+    with torch.no_grad():
+        out = m(torch.from_numpy(g["img"]))
+    assert (out - torch.from_numpy(g["logits"])).abs().max() < 1e-6
+
+
+def test_patch_embed_mirror_matches_reference_golden():
+    from vit_spectre_experiments_b200 import SpectralPatchEmbed
+
+    g = np.load(os.path.join(GOLD, "ref_patch_embed.npz"))
+    emb = SpectralPatchEmbed(16, 4, 49, 0.0, 3).eval()
+    emb.load_state_dict({k[4:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("sd::")}, strict=True)
+    with torch.no_grad():
+        assert (emb(torch.from_numpy(g["img"])) - torch.from_numpy(g["out"])).abs().max() < 1e-6
+
+
+def test_mixer_module_contract():
+    from vit_spectre_experiments_b200 import HaarDWTMix, SpectralFilterMix, SpectreViT
+
+    m = SpectralFilterMix(48, 50, 8, 48)
+    assert m.grid == (7, 7) and tuple(m.filter.shape) == (7, 4, 48, 2) and m.filter.dtype == torch.float32
+    assert list(m.state_dict()) == ["filter"]
+    m2 = copy.deepcopy(m)
+    assert torch.equal(m2.filter, m.filter) and m2.filter is not m.filter
+    m.bfloat16()
+    assert m.filter.dtype == torch.float32          # learned spectral parameters stay fp32
+    d = HaarDWTMix(512, 65, 16, 512)
+    assert tuple(d.weight.shape) == (4, 4, 4, 512) and list(d.state_dict()) == ["weight"]
+    with pytest.raises(ValueError):
+        HaarDWTMix(48, 50, 8, 48)                   # 7x7 grid is odd
+    with pytest.raises(ValueError):
+        SpectralFilterMix(48, 51, 8, 48)            # 50 tokens is not a square grid + CLS
+    vit = SpectreViT(img_size=32, patch_size=4, num_classes=100, embed_dim=64, num_encoders=3, num_heads=4,
+                     hidden_dim=96, dropout=0.0, mixer="fft")
+    keys = list(vit.state_dict())
+    assert "encoder_blocks.layers.2.mix_layer.filter" in keys
+    # clones start identical, like the reference's _get_clones (spectre.py:86)
+    assert torch.equal(vit.encoder_blocks.layers[0].mix_layer.filter, vit.encoder_blocks.layers[2].mix_layer.filter)
+
+
+def test_no_cpu_fallback():
+    from vit_spectre_experiments_b200 import SpectralFilterMix
+
+    m = SpectralFilterMix(8, 65, 2, 8)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m(torch.randn(2, 65, 8))
+
+
+def test_product_does_not_import_oracle():
+    for dirpath, _, files in os.walk(PKG):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in src and "from oracle" not in src, f

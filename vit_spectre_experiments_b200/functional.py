@@ -13,6 +13,48 @@ from . import _lib
 _DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1}
 
 
+class KernelTimer:
+    """Optional CUDA-event bracketing of every C-ABI call on the launching stream (bench.py uses it to
+    time the mixer kernels live inside the training step).  Off by default: zero overhead."""
+
+    def __init__(self):
+        self.enabled = False
+        self.records = {}   # name -> list of (start_event, end_event, meta)
+
+    def reset(self):
+        self.records = {}
+
+    def summary(self):
+        """name -> (launches, mean_ms, meta of the last call); synchronises."""
+        torch.cuda.synchronize()
+        out = {}
+        for name, evs in self.records.items():
+            ms = [s.elapsed_time(e) for s, e, _ in evs]
+            out[name] = (len(ms), sum(ms) / max(len(ms), 1), evs[-1][2])
+        return out
+
+
+TIMER = KernelTimer()
+
+
+class _timed:
+    def __init__(self, name, meta):
+        self.name, self.meta = name, meta
+
+    def __enter__(self):
+        if TIMER.enabled:
+            self.s = torch.cuda.Event(enable_timing=True)
+            self.e = torch.cuda.Event(enable_timing=True)
+            self.s.record()
+        return self
+
+    def __exit__(self, *exc):
+        if TIMER.enabled:
+            self.e.record()
+            TIMER.records.setdefault(self.name, []).append((self.s, self.e, self.meta))
+        return False
+
+
 def _act_code(t: torch.Tensor, what: str) -> int:
     if not t.is_cuda:
         raise RuntimeError(
@@ -51,8 +93,9 @@ class _FFTMix(torch.autograd.Function):
         y = torch.empty_like(x)
         B, _, E = x.shape
         with torch.cuda.device(x.device):
-            rc = lib.spectre_fftmix_fwd(x.data_ptr(), filt.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls), code,
-                                        _stream_ptr(x.device))
+            with _timed("fftmix_fwd", (B, H, W, E, x.element_size())):
+                rc = lib.spectre_fftmix_fwd(x.data_ptr(), filt.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls),
+                                            code, _stream_ptr(x.device))
         _lib.check(rc, "spectre_fftmix_fwd")
         _lib.count_launches()
         ctx.save_for_backward(x, filt)
@@ -73,9 +116,10 @@ class _FFTMix(torch.autograd.Function):
         with torch.cuda.device(x.device):
             nbytes = lib.spectre_fftmix_bwd_workspace_bytes(B, H, W, E)
             ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
-            rc = lib.spectre_fftmix_bwd(dy.data_ptr(), x.data_ptr(), filt.data_ptr(), dx.data_ptr(), dfilt.data_ptr(),
-                                        ws.data_ptr(), nbytes, B, H, W, E, int(has_cls), _act_code(x, "fft_mix"),
-                                        _stream_ptr(x.device))
+            with _timed("fftmix_bwd", (B, H, W, E, x.element_size())):
+                rc = lib.spectre_fftmix_bwd(dy.data_ptr(), x.data_ptr(), filt.data_ptr(), dx.data_ptr(),
+                                            dfilt.data_ptr(), ws.data_ptr(), nbytes, B, H, W, E, int(has_cls),
+                                            _act_code(x, "fft_mix"), _stream_ptr(x.device))
         _lib.check(rc, "spectre_fftmix_bwd")
         _lib.count_launches()
         return dx, dfilt, None, None, None
@@ -96,8 +140,9 @@ class _DWTMix(torch.autograd.Function):
         y = torch.empty_like(x)
         B, _, E = x.shape
         with torch.cuda.device(x.device):
-            rc = lib.spectre_dwtmix_fwd(x.data_ptr(), weight.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls), code,
-                                        _stream_ptr(x.device))
+            with _timed("dwtmix_fwd", (B, H, W, E, x.element_size())):
+                rc = lib.spectre_dwtmix_fwd(x.data_ptr(), weight.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls),
+                                            code, _stream_ptr(x.device))
         _lib.check(rc, "spectre_dwtmix_fwd")
         _lib.count_launches()
         ctx.save_for_backward(x, weight)
@@ -118,9 +163,10 @@ class _DWTMix(torch.autograd.Function):
         with torch.cuda.device(x.device):
             nbytes = lib.spectre_dwtmix_bwd_workspace_bytes(B, H, W, E)
             ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
-            rc = lib.spectre_dwtmix_bwd(dy.data_ptr(), x.data_ptr(), weight.data_ptr(), dx.data_ptr(), dw.data_ptr(),
-                                        ws.data_ptr(), nbytes, B, H, W, E, int(has_cls), _act_code(x, "dwt_mix"),
-                                        _stream_ptr(x.device))
+            with _timed("dwtmix_bwd", (B, H, W, E, x.element_size())):
+                rc = lib.spectre_dwtmix_bwd(dy.data_ptr(), x.data_ptr(), weight.data_ptr(), dx.data_ptr(),
+                                            dw.data_ptr(), ws.data_ptr(), nbytes, B, H, W, E, int(has_cls),
+                                            _act_code(x, "dwt_mix"), _stream_ptr(x.device))
         _lib.check(rc, "spectre_dwtmix_bwd")
         _lib.count_launches()
         return dx, dw, None, None, None

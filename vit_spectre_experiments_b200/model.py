@@ -71,6 +71,8 @@ class MHPermutMix(nn.Module):
 def build_mixer(mixer: str, d_model: int, seq_length: int, nhead: int, grid=None) -> nn.Module:
     """The one line the build changes: what ``SpectreEncoderLayer`` puts in ``mix_layer``
     (reference: ``MHPermutMix(d_model, seq_length, nhead, d_model)``, spectre.py:50)."""
+    if callable(mixer):  # any nn.Module factory with the MHPermutMix ctor contract (the slot is open)
+        return mixer(d_model, seq_length, nhead, d_model)
     if mixer == "permut":
         return MHPermutMix(d_model, seq_length, nhead, d_model)
     if mixer == "fft":

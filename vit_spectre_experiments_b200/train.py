@@ -1,0 +1,139 @@
+"""Synthetic-data, data-parallel training step around the spectral mixers.
+
+Follows the reference's single-GPU loop (``spectre_vit/repl/train.py``: model build :48-59, AdamW
+:199-201, autocast forward :219-220, CE outside autocast :226, ``zero_grad(set_to_none=True)`` /
+backward / step :235-238; KD branch :298-353) with the B200 changes SURVEY.md section 5 lists:
+bf16 autocast instead of fp16 + GradScaler, no per-step ``loss.item()`` host sync, one process per
+GPU with an NCCL gradient all-reduce (DistributedDataParallel buckets overlapped with backward --
+the only collective on the path; the reference has none).
+"""
+from __future__ import annotations
+
+import os
+from types import SimpleNamespace
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .model import SpectreViT
+
+
+def build_model(cfg: SimpleNamespace, mixer: str | None = None) -> SpectreViT:
+    """``SpectreViT`` from a reference-format config (train.py:48-59) plus the ``mixer`` key."""
+    return SpectreViT(
+        img_size=cfg.img_size, patch_size=cfg.patch_size, in_channels=cfg.in_channels, num_classes=cfg.num_classes,
+        embed_dim=cfg.embed_dim, num_encoders=cfg.num_encoders, num_heads=cfg.num_heads, hidden_dim=cfg.hidden_dim,
+        dropout=cfg.dropout, activation=cfg.activation, mixer=mixer or getattr(cfg, "mixer", "permut"),
+    )
+
+
+class TeacherViT(nn.Module):
+    """Random-init, frozen attention ViT used as the distillation teacher of config 5.  The reference
+    loads a DINOv3 backbone + linear head (``spectre_vit/distillation.py:5-22``); that third-party
+    submodule does not travel, so this is a stock ViT of the same sizes (library SDPA / cuBLAS)."""
+
+    def __init__(self, img_size=224, patch_size=16, in_channels=3, embed_dim=768, depth=12, heads=12, num_classes=1000):
+        super().__init__()
+        n = (img_size // patch_size) ** 2
+        self.patch = nn.Conv2d(in_channels, embed_dim, patch_size, patch_size)
+        self.cls = nn.Parameter(torch.zeros(1, 1, embed_dim))
+        self.pos = nn.Parameter(0.02 * torch.randn(1, n + 1, embed_dim))
+        layer = nn.TransformerEncoderLayer(embed_dim, heads, 4 * embed_dim, dropout=0.0, activation="gelu",
+                                           batch_first=True, norm_first=True)
+        self.blocks = nn.TransformerEncoder(layer, depth, enable_nested_tensor=False)
+        self.norm = nn.LayerNorm(embed_dim)
+        self.linear = nn.Linear(embed_dim, num_classes)
+
+    def forward(self, x, return_features=False):
+        t = self.patch(x).flatten(2).transpose(1, 2)
+        t = torch.cat([self.cls.expand(t.shape[0], -1, -1).to(t.dtype), t], 1) + self.pos.to(t.dtype)
+        feat = self.norm(self.blocks(t))[:, 0]
+        logits = self.linear(feat)
+        return (logits, feat) if return_features else logits
+
+
+def kd_loss(student_logits, teacher_logits, labels, T=2.0, soft_w=0.25, ce_w=0.75):
+    """``0.25 * T^2 * sum(p_T (log p_T - log_softmax(s/T))) / B + 0.75 * CE`` (train.py:334-348)."""
+    soft_t = F.softmax(teacher_logits.float() / T, dim=-1)
+    log_s = F.log_softmax(student_logits.float() / T, dim=-1)
+    soft = torch.sum(soft_t * (soft_t.clamp_min(1e-30).log() - log_s)) / log_s.shape[0] * (T * T)
+    return soft_w * soft + ce_w * F.cross_entropy(student_logits.float(), labels)
+
+
+def dist_env():
+    """(rank, local_rank, world) from torchrun's environment; (0, 0, 1) when launched plainly."""
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def init_distributed(backend: str | None = None):
+    rank, local_rank, world = dist_env()
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local_rank)
+            dist.init_process_group(backend, device_id=torch.device("cuda", local_rank))
+        else:
+            dist.init_process_group(backend)
+    return rank, local_rank, world
+
+
+class Trainer:
+    """One optimisation step = forward (autocast when ``precision == "bf16"``) -> loss -> backward
+    (DDP all-reduce overlapped) -> fused AdamW.  ``step`` returns the loss tensor without syncing."""
+
+    def __init__(self, cfg: SimpleNamespace, device, *, mixer: str | None = None, model: nn.Module | None = None,
+                 ddp: bool | None = None, seed: int | None = None):
+        self.cfg, self.device = cfg, torch.device(device)
+        torch.manual_seed(cfg.random_seed if seed is None else seed)
+        self.model = (model if model is not None else build_model(cfg, mixer)).to(self.device)
+        self.bf16 = getattr(cfg, "precision", "fp32") == "bf16" and self.device.type == "cuda"
+        self.teacher = None
+        if getattr(cfg, "distill", False):
+            self.teacher = TeacherViT(cfg.img_size, cfg.patch_size, cfg.in_channels, cfg.teacher_embed_dim,
+                                      cfg.teacher_depth, cfg.teacher_heads, cfg.num_classes).to(self.device).eval()
+            for p in self.teacher.parameters():
+                p.requires_grad_(False)
+        world = dist.get_world_size() if dist.is_initialized() else 1
+        self.world = world
+        self.net = self.model
+        if (ddp if ddp is not None else world > 1) and world > 1:
+            ids = [self.device.index] if self.device.type == "cuda" else None
+            self.net = nn.parallel.DistributedDataParallel(self.model, device_ids=ids, gradient_as_bucket_view=True,
+                                                           static_graph=True)
+        self.opt = torch.optim.AdamW(self.model.parameters(), lr=cfg.learning_rate, betas=cfg.adam_betas,
+                                     weight_decay=cfg.adam_weight_decay, fused=self.device.type == "cuda")
+
+    def synthetic_batch(self, batch: int, rank: int = 0, pinned_host: bool = False):
+        """Synthetic data of the configured shape: ``randn`` images, uniform labels, seed 42 + rank."""
+        g = torch.Generator().manual_seed(self.cfg.random_seed + rank)
+        img = torch.randn(batch, self.cfg.in_channels, self.cfg.img_size, self.cfg.img_size, generator=g)
+        lab = torch.randint(0, self.cfg.num_classes, (batch,), generator=g)
+        if pinned_host:
+            return img.pin_memory(), lab.pin_memory()
+        return img.to(self.device), lab.to(self.device)
+
+    def forward_loss(self, img, lab):
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
+            if self.teacher is None:
+                logits = self.net(img)
+            else:
+                logits, _ = self.net(img, return_features=True)
+                with torch.no_grad():
+                    t_logits = self.teacher(img)
+        if self.teacher is None:
+            return F.cross_entropy(logits.float(), lab)
+        c = self.cfg
+        return kd_loss(logits, t_logits, lab, c.distill_temperature, c.distill_soft_weight, c.distill_ce_weight)
+
+    def step(self, img, lab):
+        self.net.train()
+        loss = self.forward_loss(img, lab)
+        self.opt.zero_grad(set_to_none=True)
+        loss.backward()
+        self.opt.step()
+        return loss.detach()
