@@ -56,13 +56,14 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--only", default="")
+    ap.add_argument("--match", default="", help="substring of the shape name")
     args = ap.parse_args()
     lib = _lib.load()
     dev = torch.device("cuda:0")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     st = lambda: torch.cuda.current_stream().cuda_stream
     for name, kind, B, H, W, E, dt in SHAPES:
-        if args.only and args.only != kind:
+        if (args.only and args.only != kind) or (args.match and args.match not in name):
             continue
         T = H * W + 1
         s = 4 if dt == torch.float32 else 2
