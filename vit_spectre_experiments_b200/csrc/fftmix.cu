@@ -22,6 +22,7 @@
 // index ((g*H + h)*Wh + kw)*16 + pair, so the 16 pairs of a tile are 256 contiguous bytes
 // and every quarter-warp LDS.128/STS.128 covers all 32 banks exactly once.
 #include <cstdarg>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "fft_codelets.cuh"
@@ -348,8 +349,24 @@ int fftmix_supported(int H, int W) {
   return 0;
 }
 
+// Tensor-core (tcgen05) variants for bf16 activations live in fftmix_tc.cu.
+int fftmix_tc_supported(int H, int W, int E);
+int fftmix_tc_fwd_dispatch(const void* x, const float* filt, void* y, int B, int H, int W, int E, int cls,
+                           cudaStream_t st);
+
+// SB200_FFT_TC=0 keeps bf16 on the SIMT butterflies (A/B measurements); default is the tensor-core path.
+static bool tc_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("SB200_FFT_TC");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 int fftmix_fwd_dispatch(const void* x, const float* filt, void* y, int B, int H, int W, int E, int cls, int dtype,
                         cudaStream_t st) {
+  if (dtype == SPECTRE_DTYPE_BF16 && tc_enabled() && fftmix_tc_supported(H, W, E))
+    return fftmix_tc_fwd_dispatch(x, filt, y, B, H, W, E, cls, st);
 #define F(h, w)                                                                                     \
   if (H == h && W == w)                                                                             \
     return dtype == SPECTRE_DTYPE_F32 ? fwd_launch<h, w, float>(x, filt, y, B, E, cls, st)          \
