@@ -14,16 +14,20 @@
 //   filter          : Z = D2 * filt (fp32, per-thread registers), packed to bf16 -> A3
 //   stage 3 (cols^-1): per kw          D3[c, (h,ri)]   = A3_tmem[c, (kh,ri)] . B3
 //   stage 4 (rows^-1): per grid row h  D4[c, w]        = A4_tmem[c, (kw,ri)] . B4   (C2R incl. weights)
+//   output          : bf16 rows staged in a swizzled smem tile, written back by one TMA store.
 // Accumulation is fp32 in TMEM; the operands of every stage are bf16 (three intermediate
-// roundings + bf16 DFT matrices => ~3e-3 of max|y|, inside the 3e-2 bf16 tolerance).
+// roundings + bf16 DFT matrices => <1e-2 of max|y|, inside the 3e-2 bf16 tolerance).
 //
 // Warp roles (384 threads, one CTA per SM, persistent over images of one channel tile):
 //   warps 0-7  epilogue: warpgroup g handles half of the kw columns (stages 1-3) / half of
 //              the grid rows (stage 4); its slice of the filter lives in registers.
-//   warp  8    MMA issuer (one lane);  warp 9  TMA producer + CLS pass-through;  10-11 idle.
+//   warp  8    MMA issuer (one elected lane);  warp 9  TMA producer + CLS pass-through;  10-11 idle.
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "common.cuh"
+#include "fft_codelets.cuh"
 #include "sm100_ptx.cuh"
 
 namespace sb200 {
@@ -31,10 +35,41 @@ namespace tc {
 
 using namespace ptx;
 
+// Debug timeline: CTA 0 records clock64 at phase boundaries; slot layout [who][tile][stamp].
+//   who 0/1 = epilogue warpgroup 0/1 (first thread), 2 = MMA lane, 3 = TMA lane
+constexpr int kProfStamps = 16, kProfTiles = 8;
+#define SB200_STAMP(who, tile, idx)                                                              \
+  do {                                                                                          \
+    if (p.prof && blockIdx.x == 0 && (tile) < kProfTiles)                                       \
+      p.prof[((who) * kProfTiles + (tile)) * kProfStamps + (idx)] = clock64();                  \
+  } while (0)
+
 constexpr int kEpiThreads = 256;
 constexpr int kThreads = 384;
 constexpr int kBarCount = kEpiThreads + 32;  // named barriers: epilogue arrives, MMA warp syncs
 constexpr int kTileC = 128;
+constexpr int kEpiRegs = 216, kAuxRegs = 72;  // setmaxnreg split: 8*32*216 + 4*32*72 = 384*168 (the launch allocation)
+
+// K-major, no-swizzle B operand: byte offset of element (n, k) of an [N x K] bf16 matrix
+__host__ __device__ constexpr uint32_t bmat_off(int n, int k, int K) {
+  return (n % 8) * 16 + (n / 8) * (K / 8) * 128 + (k % 8) * 2 + (k / 8) * 128;
+}
+
+// round-to-nearest-even bf16 bit pattern of a double in the normal range (or 0), constexpr
+constexpr uint16_t bf16_bits(double v) {
+  if (v == 0.0) return 0;
+  const uint16_t sign = v < 0 ? 0x8000u : 0u;
+  double a = v < 0 ? -v : v;
+  int e = 0;
+  while (a >= 2.0) { a *= 0.5; ++e; }
+  while (a < 1.0) { a *= 2.0; --e; }
+  const double scaled = a * 128.0;                 // [128, 256)
+  int m = static_cast<int>(scaled);
+  const double frac = scaled - m;
+  if (frac > 0.5 || (frac == 0.5 && (m & 1))) ++m;
+  if (m == 256) { m = 128; ++e; }
+  return static_cast<uint16_t>(sign | ((e + 127) << 7) | (m - 128));
+}
 
 template <int H_, int W_>
 struct Cfg {
@@ -45,284 +80,395 @@ struct Cfg {
   static constexpr int K2 = (2 * H + 15) / 16 * 16;    // column-stage K and N
   static constexpr int A2C = K2 / 2;                   // TMEM columns per kw of a bf16 A operand
   static constexpr int kDCol = 0, kACol = 256;         // TMEM column bases
+  static constexpr int kFCol = 384;                    // filter bins kh >= 8 (64 columns per warpgroup)
+  static constexpr int HR = H < 8 ? H : 8;             // filter bins per kw kept in registers
   static constexpr int kHalfStride = ((HW + 16 - W) * 128 + 1023) / 1024 * 1024;  // 64-channel half
   static constexpr int kStageBytes = 2 * kHalfStride;
-  static constexpr int kStages = (kStageBytes * 4 <= 200 * 1024) ? 4 : 3;
   static constexpr int kB1 = 16 * 16 * 2, kB2 = K2 * K2 * 2;
+  static constexpr int kOffB1 = 0, kOffB4 = kB1, kOffB2 = 2 * kB1, kOffB3 = 2 * kB1 + kB2;
   static constexpr int kMatBytes = 2 * kB1 + 2 * kB2;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kMatBytes + 1024 /*align slack*/;
   // K / N slot of a half-spectrum column: warpgroup g owns slots [4g, 4g+4)
   __host__ __device__ static constexpr int slot(int kw) { return kw < KWG ? kw : 4 + (kw - KWG); }
+  __host__ __device__ static constexpr int kw_of_slot(int s) {
+    for (int q = 0; q < WH; ++q)
+      if (slot(q) == s) return q;
+    return -1;
+  }
 };
+
+// The four DFT matrices, already in their shared-memory byte layout, built at compile time.
+template <int H, int W>
+struct MatImage {
+  uint16_t w[Cfg<H, W>::kMatBytes / 2];
+};
+
+template <int H, int W>
+constexpr MatImage<H, W> make_mats() {
+  using C = Cfg<H, W>;
+  MatImage<H, W> m{};
+  for (int i = 0; i < C::kMatBytes / 2; ++i) m.w[i] = 0;
+  for (int n = 0; n < 16; ++n)
+    for (int k = 0; k < 16; ++k) {
+      // B1[n = 2*slot(kw)+ri][k = w]: forward real DFT along W
+      const int kw = C::kw_of_slot(n / 2);
+      if (kw >= 0 && k < W) {
+        const double c = cos2pi((kw * k) % W, W), s = sin2pi((kw * k) % W, W);
+        m.w[(C::kOffB1 + bmat_off(n, k, 16)) / 2] = bf16_bits(n % 2 == 0 ? c : -s);
+      }
+      // B4[n = w][k = 2*slot(kw)+ri]: C2R along W with the Hermitian weights folded in
+      const int kw4 = C::kw_of_slot(k / 2);
+      if (kw4 >= 0 && n < W) {
+        const double c = cos2pi((kw4 * n) % W, W), s = sin2pi((kw4 * n) % W, W);
+        const double wgt = (kw4 == 0 || (W % 2 == 0 && kw4 == W / 2)) ? 1.0 : 2.0;
+        m.w[(C::kOffB4 + bmat_off(n, k, 16)) / 2] = bf16_bits(k % 2 == 0 ? wgt * c : -wgt * s);
+      }
+    }
+  for (int n = 0; n < C::K2; ++n)
+    for (int k = 0; k < C::K2; ++k) {
+      // B2[n = 2kh+ri'][k = 2h+ri]: forward complex DFT along H (e^{-i phi});  B3: inverse (e^{+i phi})
+      const int a = n / 2, ra = n % 2, b = k / 2, rb = k % 2;
+      if (a < H && b < H) {
+        const double c = cos2pi((a * b) % H, H), s = sin2pi((a * b) % H, H);
+        m.w[(C::kOffB2 + bmat_off(n, k, C::K2)) / 2] = bf16_bits(ra == rb ? c : (ra == 0 ? s : -s));
+        m.w[(C::kOffB3 + bmat_off(n, k, C::K2)) / 2] = bf16_bits(ra == rb ? c : (ra == 0 ? -s : s));
+      }
+    }
+  return m;
+}
+
+template <int H, int W>
+__device__ const MatImage<H, W> g_mats = make_mats<H, W>();
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<const uint32_t*>(&h);
 }
-
-// K-major, no-swizzle B operand: element (n, k) of an [N x K] matrix
-__device__ __forceinline__ uint32_t bmat_off(int n, int k, int K) {
-  return (n % 8) * 16 + (n / 8) * (K / 8) * 128 + (k % 8) * 2 + (k / 8) * 128;
+__device__ __forceinline__ float f32(uint32_t u) { return __uint_as_float(u); }
+__device__ __forceinline__ void st_shared_u16(uint32_t saddr, uint32_t v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(saddr), "h"(static_cast<unsigned short>(v)) : "memory");
 }
 
-// cos/sin of 2*pi*num/den with exact argument reduction
-__device__ __forceinline__ void cs2pi(int num, int den, float& c, float& s) {
-  sincospif(2.0f * static_cast<float>(num % den) / static_cast<float>(den), &s, &c);
-}
-
+// byte offset of (token row r, channel m of the 128-wide tile) in a [2 halves][rows][64 ch] 128B-swizzled tile
 template <class C>
-__device__ void build_matrices(uint8_t* sB1, uint8_t* sB2, uint8_t* sB3, uint8_t* sB4, bool conj_dir) {
-  constexpr int H = C::H, W = C::W, WH = C::WH, K2 = C::K2;
-  (void)conj_dir;
-  auto put = [](uint8_t* base, uint32_t off, float v) { *reinterpret_cast<__nv_bfloat16*>(base + off) = __float2bfloat16(v); };
-  // B1[n = 2*slot(kw)+ri][k = w]: forward real DFT along W
-  for (int i = threadIdx.x; i < 16 * 16; i += blockDim.x) {
-    const int n = i / 16, k = i % 16;
-    float v = 0.f;
-    const int sl = n / 2, ri = n % 2;
-    int kw = -1;
-    for (int q = 0; q < WH; ++q) if (C::slot(q) == sl) kw = q;
-    if (kw >= 0 && k < W) {
-      float c, s; cs2pi(kw * k, W, c, s);
-      v = ri == 0 ? c : -s;
-    }
-    put(sB1, bmat_off(n, k, 16), v);
-    // B4[n = w][k = 2*slot(kw)+ri]: C2R along W with the Hermitian weights folded in
-    float u = 0.f;
-    const int sl4 = k / 2, ri4 = k % 2;
-    int kw4 = -1;
-    for (int q = 0; q < WH; ++q) if (C::slot(q) == sl4) kw4 = q;
-    if (kw4 >= 0 && n < W) {
-      float c, s; cs2pi(kw4 * n, W, c, s);
-      const float wgt = (kw4 == 0 || (W % 2 == 0 && kw4 == W / 2)) ? 1.f : 2.f;
-      u = ri4 == 0 ? wgt * c : -wgt * s;
-    }
-    put(sB4, bmat_off(n, k, 16), u);
-  }
-  // B2[n = 2kh+ri'][k = 2h+ri]: forward complex DFT along H;  B3: inverse
-  for (int i = threadIdx.x; i < K2 * K2; i += blockDim.x) {
-    const int n = i / K2, k = i % K2;
-    float f = 0.f, g = 0.f;
-    const int a = n / 2, ra = n % 2, b = k / 2, rb = k % 2;
-    if (a < H && b < H) {
-      float c, s; cs2pi(a * b, H, c, s);
-      // forward e^{-i phi}: re' = a cos + b sin ; im' = -a sin + b cos
-      f = (ra == rb) ? c : (ra == 0 ? s : -s);
-      // inverse e^{+i phi}: re' = a cos - b sin ; im' = a sin + b cos
-      g = (ra == rb) ? c : (ra == 0 ? -s : s);
-    }
-    put(sB2, bmat_off(n, k, K2), f);
-    put(sB3, bmat_off(n, k, K2), g);
-  }
+__device__ __forceinline__ uint32_t tile_off(int r, int m) {
+  return (m >> 6) * C::kHalfStride + r * 128 + (((((m & 63) >> 3) ^ (r & 7))) << 4) + (m & 7) * 2;
 }
+
+template <int H_, int W_>
+struct FwdSmem {
+  using C = Cfg<H_, W_>;
+  static constexpr int kBudget = 220 * 1024;
+  static constexpr int kFit = (kBudget - C::kMatBytes) / C::kStageBytes - 1;   // input stages next to one output tile
+  static constexpr int kStages = kFit > 4 ? 4 : kFit;
+  static_assert(kStages >= 2, "forward: need at least two input stages");
+  static constexpr int kOut = kStages * C::kStageBytes;
+  static constexpr int kMat = kOut + C::kStageBytes;
+  static constexpr int kBytes = kMat + C::kMatBytes + 1024 /*alignment slack*/;
+};
 
 struct FwdParams {
   const __nv_bfloat16* x;
   const float* filt;
   __nv_bfloat16* y;
   int B, E, cls, nct, img_stride;
+  long long* prof;   // optional per-phase clock64 stamps of CTA 0 (debug; null in production)
 };
 
 template <int H, int W>
 __global__ void __launch_bounds__(kThreads, 1)
-fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const FwdParams p) {
+fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y,
+                     const FwdParams p) {
   using C = Cfg<H, W>;
-  constexpr int WH = C::WH, KWG = C::KWG, HG = C::HG, K2 = C::K2, A2C = C::A2C, S = C::kStages;
+  using SM = FwdSmem<H, W>;
+  constexpr int WH = C::WH, KWG = C::KWG, HG = C::HG, K2 = C::K2, A2C = C::A2C, S = SM::kStages;
+  constexpr int WP = (W + 1) / 2;   // packed bf16 pairs per output row
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sB1 = smem + S * C::kStageBytes;
-  uint8_t* sB4 = sB1 + C::kB1;
-  uint8_t* sB2 = sB4 + C::kB1;
-  uint8_t* sB3 = sB2 + C::kB2;
+  uint8_t* sOut = smem + SM::kOut;
+  uint8_t* sMat = smem + SM::kMat;
   __shared__ uint64_t full_bar[S], empty_bar[S], dready_bar[4];
   __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) uint8_t sDummy[8 * 16];   // sink for the padded rows of stmatrix
 
+  const long long t_start = clock64();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ct = blockIdx.x % p.nct;
   const int img0 = blockIdx.x / p.nct;
   const int c0 = ct * kTileC;
-  const int T = C::HW + p.cls;
   const int ntiles = img0 < p.B ? (p.B - img0 + p.img_stride - 1) / p.img_stride : 0;
+  const bool half1 = c0 + 64 < p.E;
 
   // ---- one-time setup
   if (warp == 8) tmem_alloc<512>(&tmem_base_s);
   if (tid == 9 * 32) {
     prefetch_tensormap(&tmap_x);
+    prefetch_tensormap(&tmap_y);
     for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int k = 0; k < 4; ++k) mbar_init(&dready_bar[k], 1);
     mbar_fence_init();
+    // prologue loads: fill the input ring before the CTA-wide setup barrier (only the barriers are needed)
+    const uint32_t bytes0 = (half1 ? 2u : 1u) * C::HW * 128u;
+    for (int it = 0; it < S && it < ntiles; ++it) {
+      uint8_t* dst = smem + it * C::kStageBytes;
+      const int b = img0 + it * p.img_stride;
+      mbar_arrive_expect_tx(&full_bar[it], bytes0);
+      tma_load_3d(dst, &tmap_x, &full_bar[it], c0, 0, b);
+      if (half1) tma_load_3d(dst + C::kHalfStride, &tmap_x, &full_bar[it], c0 + 64, 0, b);
+    }
   }
-  build_matrices<C>(sB1, sB2, sB3, sB4, false);
-  // rows past the image in every half (read by the last row's K=16 window) must be finite
-  for (int i = tid; i < S * 2 * ((C::kHalfStride - C::HW * 128) / 16); i += kThreads) {
+  // epilogue threads: issue the loads of their filter slice now so the latency overlaps the setup
+  float2 Fld[KWG][H];
+  if (warp < 8) {
+    const int g = warp >> 2, c = c0 + (warp & 3) * 32 + lane;
+    const bool cvalid = c < p.E;
+    const float scale = 1.0f / static_cast<float>(H * W);
+    const float2* fp = reinterpret_cast<const float2*>(p.filt) + (cvalid ? c : 0);
+#pragma unroll
+    for (int j = 0; j < KWG; ++j) {
+      const int kw = g * KWG + j;
+      const bool ok = kw < WH && cvalid;
+#pragma unroll
+      for (int kh = 0; kh < H; ++kh) {
+        float2 f = make_float2(0.f, 0.f);
+        if (ok) f = __ldg(fp + (static_cast<size_t>(kh) * WH + kw) * p.E);
+        Fld[j][kh] = make_float2(f.x * scale, f.y * scale);
+      }
+    }
+  }
+  for (int i = tid; i < C::kMatBytes / 16; i += kThreads)
+    reinterpret_cast<uint4*>(sMat)[i] = reinterpret_cast<const uint4*>(g_mats<H, W>.w)[i];
+  // rows past the image in every input half (read by the last grid row's K=16 window) must be finite
+  {
     constexpr int per = (C::kHalfStride - C::HW * 128) / 16;
-    const int half = i / per, j = i % per;
-    reinterpret_cast<uint4*>(smem + half * C::kHalfStride + C::HW * 128)[j] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < S * 2 * per; i += kThreads)
+      reinterpret_cast<uint4*>(smem + (i / per) * C::kHalfStride + C::HW * 128)[i % per] = make_uint4(0, 0, 0, 0);
   }
   fence_proxy_async_smem();
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tbase = tmem_base_s;
+  if (tid == 0 && p.prof && blockIdx.x == 0) { p.prof[14] = t_start; p.prof[15] = clock64(); }
 
   if (warp < 8) {
     // =========================================================== epilogue warpgroups
-    setmaxnreg_inc<224>();
+    setmaxnreg_inc<kEpiRegs>();
     const int g = warp >> 2;                                   // warpgroup
     const int m = (warp & 3) * 32 + lane;                      // TMEM lane = channel in tile
     const int c = c0 + m;
     const bool cvalid = c < p.E;
+    const bool stamp = lane == 0 && (warp & 3) == 0;
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const uint32_t tD = tbase + lane_off + C::kDCol;
     const uint32_t tA = tbase + lane_off + C::kACol;
 
-    // filter slice of this thread: F[j][kh] for kw = g*KWG + j, pre-scaled by the ortho 1/(H*W)
-    float2 F[KWG][H];
-    {
-      const float scale = 1.0f / static_cast<float>(H * W);
+    // filter slice of this thread, pre-scaled by the ortho 1/(H*W): bins kh < 8 of kw = g*KWG + j
+    // stay in registers, bins kh >= 8 are parked in spare TMEM columns of the thread's own lane
+    // (16 columns per kw, read back next to the D2 loads) - 112 live filter registers would spill.
+    // (The global loads were issued before the setup barrier; see `Fld` above.)
+    float2 FR[KWG][C::HR];
+    const uint32_t tF = tbase + lane_off + C::kFCol + g * 64;
 #pragma unroll
-      for (int j = 0; j < KWG; ++j) {
-        const int kw = g * KWG + j;
+    for (int j = 0; j < KWG; ++j) {
 #pragma unroll
-        for (int kh = 0; kh < H; ++kh) {
-          float2 f = make_float2(0.f, 0.f);
-          if (kw < WH && cvalid) {
-            f = __ldg(reinterpret_cast<const float2*>(p.filt) + (static_cast<size_t>(kh) * WH + kw) * p.E + c);
-            f.x *= scale; f.y *= scale;
-          }
-          F[j][kh] = f;
+      for (int kh = 0; kh < C::HR; ++kh) FR[j][kh] = Fld[j][kh];
+      if (H > 8) {
+        uint32_t hi[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) hi[q] = 0u;
+#pragma unroll
+        for (int kh = 8; kh < H; ++kh) {
+          hi[2 * (kh - 8)] = __float_as_uint(Fld[j][kh].x);
+          hi[2 * (kh - 8) + 1] = __float_as_uint(Fld[j][kh].y);
         }
+        tmem_st16(tF + j * 16, hi);
       }
     }
+    if (H > 8) tmem_wait_st();
+    if (tid == 0 && p.prof && blockIdx.x == 0) p.prof[13] = clock64();
 
     for (int it = 0; it < ntiles; ++it) {
       const uint32_t par = it & 1;
       const int b = img0 + it * p.img_stride;
       // ---------------- E1: D1[h][slot,ri] -> A2[kw][h] (bf16 pairs)
+      if (stamp) SB200_STAMP(g, it, 0);
       mbar_wait(&dready_bar[0], par);
       tc_fence_after_sync();
+      if (stamp) SB200_STAMP(g, it, 1);
       {
-        uint32_t pk[KWG][A2C];
+        // A2C is a multiple of 4: each batch of 4 grid rows becomes one 4-column store per kw
 #pragma unroll
-        for (int hb = 0; hb < H; hb += 4) {
+        for (int hb = 0; hb < A2C; hb += 4) {
           uint32_t v[4][8];
 #pragma unroll
           for (int i = 0; i < 4; ++i)
             if (hb + i < H) tmem_ld8(tD + (hb + i) * 16 + 8 * g, v[i]);
           tmem_wait_ld();
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            if (hb + i < H) {
+          for (int j = 0; j < KWG; ++j) {
+            uint32_t pk[4];
 #pragma unroll
-              for (int j = 0; j < KWG; ++j)
-                pk[j][hb + i] = pack_bf16(__uint_as_float(v[i][2 * j]), __uint_as_float(v[i][2 * j + 1]));
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < KWG; ++j) {
-#pragma unroll
-          for (int q = H; q < A2C; ++q) pk[j][q] = 0u;
-          const int kw = g * KWG + j;
-          if (kw < WH) tmem_st<A2C>(tA + kw * A2C, pk[j]);
+            for (int i = 0; i < 4; ++i)
+              pk[i] = (hb + i < H) ? pack_bf16(f32(v[i][2 * j]), f32(v[i][2 * j + 1])) : 0u;
+            const int kw = g * KWG + j;
+            if (kw < WH) tmem_st4(tA + kw * A2C + hb, pk);
+          }
         }
         tmem_wait_st();
         tc_fence_before_sync();
         named_bar_arrive(1, kBarCount);
       }
-      // ---------------- E2: Z = D2 * filter -> A3[kw][kh]
+      if (stamp) SB200_STAMP(g, it, 2);
+      // ---------------- E2: Z = D2 * filter -> A3[kw][kh]   (loads double-buffered)
       mbar_wait(&dready_bar[1], par);
       tc_fence_after_sync();
+      if (stamp) SB200_STAMP(g, it, 3);
+      {
+        // 16-column units (8 complex bins), double-buffered: unit u = (kw_local, half)
+        constexpr int UPK = K2 / 16, NU = KWG * UPK;
+        uint32_t v[2][16];
+        uint32_t ft[16];
+        if (g * KWG < WH) tmem_ld16(tD + (g * KWG) * K2, v[0]);
 #pragma unroll
-      for (int j = 0; j < KWG; ++j) {
-        const int kw = g * KWG + j;
-        if (kw < WH) {
-          uint32_t v[K2];
-          tmem_ld<K2>(tD + kw * K2, v);
+        for (int u = 0; u < NU; ++u) {
+          const int j = u / UPK, hf = u % UPK;
+          const int kw = g * KWG + j;
           tmem_wait_ld();
-          uint32_t z[A2C];
-#pragma unroll
-          for (int kh = 0; kh < H; ++kh) {
-            const float re = __uint_as_float(v[2 * kh]), im = __uint_as_float(v[2 * kh + 1]);
-            const float2 f = F[j][kh];
-            z[kh] = pack_bf16(re * f.x - im * f.y, re * f.y + im * f.x);
+          if (u + 1 < NU) {
+            const int kwn = g * KWG + (u + 1) / UPK;
+            if (kwn < WH) {
+              tmem_ld16(tD + kwn * K2 + ((u + 1) % UPK) * 16, v[(u + 1) & 1]);
+              if ((u + 1) % UPK == 1) tmem_ld16(tF + ((u + 1) / UPK) * 16, ft);
+            }
           }
+          if (kw < WH) {
+            uint32_t z[8];
 #pragma unroll
-          for (int q = H; q < A2C; ++q) z[q] = 0u;
-          tmem_st<A2C>(tA + kw * A2C, z);
+            for (int q = 0; q < 8; ++q) {
+              const int kh = hf * 8 + q;
+              if (kh < H) {
+                const float re = f32(v[u & 1][2 * q]), im = f32(v[u & 1][2 * q + 1]);
+                const float2 f = hf == 0 ? FR[j][q < C::HR ? q : 0] : make_float2(f32(ft[2 * q]), f32(ft[2 * q + 1]));
+                z[q] = pack_bf16(re * f.x - im * f.y, re * f.y + im * f.x);
+              } else {
+                z[q] = 0u;
+              }
+            }
+            tmem_st8(tA + kw * A2C + hf * 8, z);
+          }
         }
       }
       tmem_wait_st();
       tc_fence_before_sync();
       named_bar_arrive(2, kBarCount);
+      if (stamp) SB200_STAMP(g, it, 4);
       // ---------------- E3: D3[kw][h,ri] -> A4[h][slot]
       mbar_wait(&dready_bar[2], par);
       tc_fence_after_sync();
+      if (stamp) SB200_STAMP(g, it, 5);
       {
-        uint32_t pk[H][4];
+        // two kw columns at a time: their (re, im) pairs go to adjacent K slots of every grid row
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int kw = g * KWG + j;
-          if (j < KWG && kw < WH) {
-            uint32_t v[K2];
-            tmem_ld<K2>(tD + kw * K2, v);
-            tmem_wait_ld();
+        for (int jp = 0; jp < 4; jp += 2) {
+          const int kw0 = g * KWG + jp, kw1 = kw0 + 1;
+          const bool live0 = jp < KWG && kw0 < WH, live1 = jp + 1 < KWG && kw1 < WH;
+          uint32_t v0[K2], v1[K2];
+          if (live0) tmem_ld<K2>(tD + kw0 * K2, v0);
+          if (live1) tmem_ld<K2>(tD + kw1 * K2, v1);
+          tmem_wait_ld();
 #pragma unroll
-            for (int h = 0; h < H; ++h) pk[h][j] = pack_bf16(__uint_as_float(v[2 * h]), __uint_as_float(v[2 * h + 1]));
-          } else {
-#pragma unroll
-            for (int h = 0; h < H; ++h) pk[h][j] = 0u;
-          }
+          for (int h = 0; h < H; ++h)
+            tmem_st2(tA + h * 8 + 4 * g + jp, live0 ? pack_bf16(f32(v0[2 * h]), f32(v0[2 * h + 1])) : 0u,
+                     live1 ? pack_bf16(f32(v1[2 * h]), f32(v1[2 * h + 1])) : 0u);
         }
-#pragma unroll
-        for (int h = 0; h < H; ++h) tmem_st4(tA + h * 8 + 4 * g, pk[h]);
         tmem_wait_st();
         tc_fence_before_sync();
         named_bar_arrive(3, kBarCount);
       }
-      // ---------------- E4: D4[h][w] -> y
+      if (stamp) SB200_STAMP(g, it, 6);
+      // ---------------- E4: D4[h][w] -> bf16 -> swizzled smem tile -> TMA store
+      if (tid == 0) tma_store_wait_read<0>();          // previous tile's store has drained sOut
       mbar_wait(&dready_bar[3], par);
       tc_fence_after_sync();
+      if (stamp) SB200_STAMP(g, it, 7);
       {
-        uint32_t v[HG][16];
-#pragma unroll
-        for (int i = 0; i < HG; ++i)
-          if (g * HG + i < H) tmem_ld16(tD + (g * HG + i) * 16, v[i]);
-        tmem_wait_ld();
-        tc_fence_before_sync();
-        if (it + 1 < ntiles) named_bar_arrive(4, kBarCount);   // D region free for the next tile
-        if (cvalid) {
-          __nv_bfloat16* yb = p.y + (static_cast<size_t>(b) * T + p.cls) * p.E + c;
+        // TMEM is read in the mma C-fragment shape (thread = 2 adjacent tokens of one channel), packed to
+        // bf16 pairs and transposed into the token-major output tile by stmatrix.trans: one instruction
+        // moves a [8 tokens x 32 channels] block.  Lane T supplies the row address of matrix T/8, row T%8.
+        const int q = warp & 3;
+        const int mi = lane >> 3, rep = mi >> 1, up = mi & 1;
+        const int wtok = rep * 8 + (lane & 7);                       // grid column this lane addresses
+        const bool wvalid = wtok < W;
+        const uint32_t obase = smem_u32(sOut) + (q >> 1) * C::kHalfStride;
+        const uint32_t chunk0 = static_cast<uint32_t>(4 * (q & 1) + up);         // channels 32q + 8up + [0,8)
+        const uint32_t dummy = smem_u32(sDummy) + (warp & 7) * 16;
+        auto stage4 = [&](auto gc) {
+          constexpr int G = decltype(gc)::value;
+          constexpr int h0 = G * HG;
+          uint32_t a[2][8], bq[2][8];
+          if (h0 < H) {
+            tmem_ld_16x256b_x2(tD + h0 * 16, a[0]);
+            tmem_ld_16x256b_x2(tD + (16u << 16) + h0 * 16, bq[0]);
+          }
+          named_bar_sync(5, kEpiThreads);                        // sOut free (thread 0 waited above)
 #pragma unroll
           for (int i = 0; i < HG; ++i) {
-            const int h = g * HG + i;
-            if (h < H) {
-#pragma unroll
-              for (int w = 0; w < W; ++w)
-                __stcs(reinterpret_cast<unsigned short*>(yb + static_cast<size_t>(h * W + w) * p.E),
-                       __bfloat16_as_ushort(__float2bfloat16(__uint_as_float(v[i][w]))));
+            if (h0 + i < H) {
+              tmem_wait_ld();
+              if (i + 1 < HG && h0 + i + 1 < H) {
+                tmem_ld_16x256b_x2(tD + (h0 + i + 1) * 16, a[(i + 1) & 1]);
+                tmem_ld_16x256b_x2(tD + (16u << 16) + (h0 + i + 1) * 16, bq[(i + 1) & 1]);
+              }
+              const int t = (h0 + i) * W + wtok;
+              const uint32_t row = obase + t * 128;
+              const uint32_t x7 = static_cast<uint32_t>(t & 7);
+              const uint32_t ad0 = wvalid ? row + ((chunk0 ^ x7) << 4) : dummy;
+              const uint32_t ad1 = wvalid ? row + (((chunk0 + 2) ^ x7) << 4) : dummy;
+              const uint32_t* u = a[i & 1];
+              const uint32_t* w2 = bq[i & 1];
+              stmatrix_x4_trans(ad0, pack_bf16(f32(u[0]), f32(u[1])), pack_bf16(f32(u[2]), f32(u[3])),
+                                pack_bf16(f32(u[4]), f32(u[5])), pack_bf16(f32(u[6]), f32(u[7])));
+              stmatrix_x4_trans(ad1, pack_bf16(f32(w2[0]), f32(w2[1])), pack_bf16(f32(w2[2]), f32(w2[3])),
+                                pack_bf16(f32(w2[4]), f32(w2[5])), pack_bf16(f32(w2[6]), f32(w2[7])));
             }
           }
+          tc_fence_before_sync();
+          if (it + 1 < ntiles) named_bar_arrive(4, kBarCount);   // D region free for the next tile
+          if (stamp) SB200_STAMP(G, it, 8);
+        };
+        if (g == 0) stage4(std::integral_constant<int, 0>{});
+        else stage4(std::integral_constant<int, 1>{});
+        fence_proxy_async_smem();
+        named_bar_sync(6, kEpiThreads);
+        if (tid == 0) {
+          tma_store_3d(&tmap_y, sOut, c0, 0, b);
+          if (half1) tma_store_3d(&tmap_y, sOut + C::kHalfStride, c0 + 64, 0, b);
+          tma_store_commit();
+          if (it + 1 == ntiles) tma_store_wait_all<0>();   // smem must outlive the last store
         }
       }
+      if (stamp) SB200_STAMP(g, it, 9);
     }
   } else {
-    setmaxnreg_dec<56>();
+    setmaxnreg_dec<kAuxRegs>();
     if (warp == 8) {
       // ========================================================= MMA issuer
       const uint32_t tD = tbase + C::kDCol, tA = tbase + C::kACol;
       const uint32_t id_row = umma_idesc_bf16(128, 16, 1, 0);
       const uint32_t id_col = umma_idesc_bf16(128, K2, 0, 0);
       const uint32_t id_irow = umma_idesc_bf16(128, 16, 0, 0);
-      const uint64_t b1 = umma_smem_desc(smem_u32(sB1), 128, 256, kSwzNone);
-      const uint64_t b4 = umma_smem_desc(smem_u32(sB4), 128, 256, kSwzNone);
-      const uint64_t b2 = umma_smem_desc(smem_u32(sB2), 128, (K2 / 8) * 128, kSwzNone);
-      const uint64_t b3 = umma_smem_desc(smem_u32(sB3), 128, (K2 / 8) * 128, kSwzNone);
+      const uint64_t b1 = umma_smem_desc(smem_u32(sMat + C::kOffB1), 128, 256, kSwzNone);
+      const uint64_t b4 = umma_smem_desc(smem_u32(sMat + C::kOffB4), 128, 256, kSwzNone);
+      const uint64_t b2 = umma_smem_desc(smem_u32(sMat + C::kOffB2), 128, (K2 / 8) * 128, kSwzNone);
+      const uint64_t b3 = umma_smem_desc(smem_u32(sMat + C::kOffB3), 128, (K2 / 8) * 128, kSwzNone);
       for (int it = 0; it < ntiles; ++it) {
         const int s = it % S;
+        if (lane == 0) SB200_STAMP(2, it, 0);
         mbar_wait(&full_bar[s], (it / S) & 1);
         if (it > 0) named_bar_sync(4, kBarCount);
         tc_fence_after_sync();
-        if (lane == 0) {
+        if (lane == 0) SB200_STAMP(2, it, 1);
+        if (elect_one()) {
           const uint64_t a0 = umma_smem_desc(smem_u32(smem + s * C::kStageBytes), C::kHalfStride, 1024, kSwz128);
 #pragma unroll
           for (int h = 0; h < H; ++h) umma_ss(tD + h * 16, a0 + static_cast<uint64_t>(h * W * 8), b1, id_row, 0);
@@ -330,9 +476,11 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const FwdParams
           umma_commit(&dready_bar[0]);
         }
         __syncwarp();
+        if (lane == 0) SB200_STAMP(2, it, 2);
         named_bar_sync(1, kBarCount);
         tc_fence_after_sync();
-        if (lane == 0) {
+        if (lane == 0) SB200_STAMP(2, it, 3);
+        if (elect_one()) {
 #pragma unroll
           for (int kw = 0; kw < WH; ++kw)
 #pragma unroll
@@ -341,9 +489,11 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const FwdParams
           umma_commit(&dready_bar[1]);
         }
         __syncwarp();
+        if (lane == 0) SB200_STAMP(2, it, 4);
         named_bar_sync(2, kBarCount);
         tc_fence_after_sync();
-        if (lane == 0) {
+        if (lane == 0) SB200_STAMP(2, it, 5);
+        if (elect_one()) {
 #pragma unroll
           for (int kw = 0; kw < WH; ++kw)
 #pragma unroll
@@ -352,24 +502,28 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const FwdParams
           umma_commit(&dready_bar[2]);
         }
         __syncwarp();
+        if (lane == 0) SB200_STAMP(2, it, 6);
         named_bar_sync(3, kBarCount);
         tc_fence_after_sync();
-        if (lane == 0) {
+        if (lane == 0) SB200_STAMP(2, it, 7);
+        if (elect_one()) {
 #pragma unroll
           for (int h = 0; h < H; ++h) umma_ts(tD + h * 16, tA + h * 8, b4, id_irow, 0);
           umma_commit(&dready_bar[3]);
         }
         __syncwarp();
+        if (lane == 0) SB200_STAMP(2, it, 8);
       }
     } else if (warp == 9) {
       // ========================================================= TMA producer + CLS pass-through
-      const bool half1 = c0 + 64 < p.E;
+      const int T = C::HW + p.cls;
       const uint32_t bytes = (half1 ? 2u : 1u) * C::HW * 128u;
       for (int it = 0; it < ntiles; ++it) {
         const int s = it % S;
         const int b = img0 + it * p.img_stride;
         if (it >= S) mbar_wait(&empty_bar[s], ((it / S) - 1) & 1);
-        if (lane == 0) {
+        if (lane == 0 && it >= S) {
+          SB200_STAMP(3, it, 0);
           uint8_t* dst = smem + s * C::kStageBytes;
           mbar_arrive_expect_tx(&full_bar[s], bytes);
           tma_load_3d(dst, &tmap_x, &full_bar[s], c0, 0, b);
@@ -428,31 +582,38 @@ static void plan_grid(int B, int E, int* nct, int* img_stride) {
   *img_stride = per;
 }
 
+static long long* g_prof = nullptr;
+void set_profile_buffer(long long* dev) { g_prof = dev; }
+
 template <int H, int W>
 static int fwd_launch(const void* x, const float* filt, void* y, int B, int E, int cls, cudaStream_t st) {
   using C = Cfg<H, W>;
+  using SM = FwdSmem<H, W>;
   auto kern = fftmix_tc_fwd_kernel<H, W>;
   static bool configured = false;
   if (!configured) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes) != cudaSuccess)
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kBytes) != cudaSuccess)
       return fail(SPECTRE_E_CUDA, "cudaFuncSetAttribute(tc fwd): %s", cudaGetErrorString(cudaGetLastError()));
     configured = true;
   }
-  CUtensorMap tmap;
-  if (int rc = make_token_map(&tmap, x, B, C::HW, C::HW + cls, E, cls)) return rc;
+  CUtensorMap tmx, tmy;
+  if (int rc = make_token_map(&tmx, x, B, C::HW, C::HW + cls, E, cls)) return rc;
+  if (int rc = make_token_map(&tmy, y, B, C::HW, C::HW + cls, E, cls)) return rc;
   FwdParams p;
   p.x = static_cast<const __nv_bfloat16*>(x);
   p.filt = filt;
   p.y = static_cast<__nv_bfloat16*>(y);
   p.B = B; p.E = E; p.cls = cls;
+  p.prof = g_prof;
   plan_grid(B, E, &p.nct, &p.img_stride);
-  kern<<<p.nct * p.img_stride, kThreads, C::kSmemBytes, st>>>(tmap, p);
+  kern<<<p.nct * p.img_stride, kThreads, SM::kBytes, st>>>(tmx, tmy, p);
   last_launch_count() = 1;
   const cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "fftmix_tc_fwd launch: %s", cudaGetErrorString(err));
   return SPECTRE_OK;
 }
 
+//PART4
 }  // namespace tc
 
 // (H, W) grids with a tensor-core kernel; E must be a multiple of 8 (16-byte TMA strides)
@@ -475,3 +636,7 @@ int fftmix_tc_fwd_dispatch(const void* x, const float* filt, void* y, int B, int
 }
 
 }  // namespace sb200
+
+// Debug hook (not part of include/spectre_b200.h): device buffer of 6*8*16 int64 that CTA 0 of the
+// tensor-core kernels fills with clock64 stamps; nullptr switches it off.
+extern "C" void spectre_debug_tc_profile(long long* dev_buffer) { sb200::tc::set_profile_buffer(dev_buffer); }
