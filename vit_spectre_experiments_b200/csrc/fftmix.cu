@@ -353,6 +353,9 @@ int fftmix_supported(int H, int W) {
 int fftmix_tc_supported(int H, int W, int E);
 int fftmix_tc_fwd_dispatch(const void* x, const float* filt, void* y, int B, int H, int W, int E, int cls,
                            cudaStream_t st);
+int fftmix_tc_bwd_dispatch(const void* dy, const void* x, const float* filt, void* dx, float* dfilt, void* ws,
+                           size_t ws_bytes, int B, int H, int W, int E, int cls, cudaStream_t st);
+size_t fftmix_tc_bwd_workspace(int B, int H, int W, int E);
 
 // SB200_FFT_TC=0 keeps bf16 on the SIMT butterflies (A/B measurements); default is the tensor-core path.
 static bool tc_enabled() {
@@ -378,6 +381,8 @@ int fftmix_fwd_dispatch(const void* x, const float* filt, void* y, int B, int H,
 
 int fftmix_bwd_dispatch(const void* dy, const void* x, const float* filt, void* dx, float* dfilt, void* ws,
                         size_t ws_bytes, int B, int H, int W, int E, int cls, int dtype, cudaStream_t st) {
+  if (dtype == SPECTRE_DTYPE_BF16 && tc_enabled() && fftmix_tc_supported(H, W, E))
+    return fftmix_tc_bwd_dispatch(dy, x, filt, dx, dfilt, ws, ws_bytes, B, H, W, E, cls, st);
 #define F(h, w)                                                                                                      \
   if (H == h && W == w)                                                                                              \
     return dtype == SPECTRE_DTYPE_F32 ? bwd_launch<h, w, float>(dy, x, filt, dx, dfilt, ws, ws_bytes, B, E, cls, st) \
@@ -397,8 +402,12 @@ size_t fftmix_bwd_workspace(int B, int H, int W, int E) {
   }
   SB200_FFT_GRIDS(F)
 #undef F
-  if (ny <= 1) return 0;
-  return static_cast<size_t>(ny) * H * (W / 2 + 1) * E * 2 * sizeof(float);
+  size_t need = ny <= 1 ? 0 : static_cast<size_t>(ny) * H * (W / 2 + 1) * E * 2 * sizeof(float);
+  if (tc_enabled() && fftmix_tc_supported(H, W, E)) {
+    const size_t t = fftmix_tc_bwd_workspace(B, H, W, E);
+    if (t > need) need = t;
+  }
+  return need;
 }
 
 }  // namespace sb200

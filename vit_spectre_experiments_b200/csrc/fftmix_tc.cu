@@ -582,6 +582,16 @@ static void plan_grid(int B, int E, int* nct, int* img_stride) {
   *img_stride = per;
 }
 
+// backward: 64-channel blocks x image-pair groups
+static void plan_bwd_grid(int B, int E, int* nblk, int* pair_stride) {
+  *nblk = (E + 63) / 64;
+  const int npairs = (B + 1) / 2;
+  int per = device_sm_count() / *nblk;
+  if (per < 1) per = 1;
+  if (per > npairs) per = npairs;
+  *pair_stride = per;
+}
+
 static long long* g_prof = nullptr;
 void set_profile_buffer(long long* dev) { g_prof = dev; }
 
@@ -613,7 +623,519 @@ static int fwd_launch(const void* x, const float* filt, void* y, int B, int E, i
   return SPECTRE_OK;
 }
 
-//PART4
+// =====================================================================================================
+// Backward:  dx = irfft2(conj(filt) * rfft2(dy)),  dfilt = sum_b conj(rfft2(x_b)) * (c * rfft2(dy_b))
+// (SURVEY.md section 8 row A4).  Tile = TWO images x 64 channels (lanes 0-63 = image 2p, 64-127 = image
+// 2p+1), so the 64-channel filter slice fits in shared memory (fp32) next to the dy / x / dx tiles and the
+// filter-gradient accumulators fit in registers (each thread owns 4 of the 8 kw slots of its channel).
+//   phases per tile (MMA -> epilogue):  rows(dy) -> A_dy | rows(x) -> A_x | cols(dy,x; slots 0-3) -> acc, Z |
+//                                       cols(dy,x; slots 4-7) -> acc, Z | cols^-1(Z) -> A4 | rows^-1 -> dx
+//   TMEM: D [0,256)  A_dy/Z [256,384)  A_x/A4 [384,512)
+template <int H_, int W_>
+struct BwdSmem {
+  using C = Cfg<H_, W_>;
+  static constexpr int kSlotF = (2 * H_ + 3) / 4 * 4;                // floats per slot (16-byte aligned)
+  static constexpr int kFiltStride = 8 * kSlotF + 4;                 // floats per channel (8 slots, padded)
+  static constexpr int kDy = 0, kX = C::kStageBytes, kOut = 2 * C::kStageBytes;
+  static constexpr int kFilt = 3 * C::kStageBytes;
+  static constexpr int kFiltBytes = 64 * kFiltStride * 4;
+  static constexpr int kMat = kFilt + kFiltBytes;
+  static constexpr int kBytes = kMat + C::kMatBytes + 1024;
+  static_assert(kBytes <= 227 * 1024, "backward shared-memory budget");
+};
+
+struct BwdParams {
+  const __nv_bfloat16* dy;
+  const float* filt;
+  __nv_bfloat16* dx;
+  float* part;         // [slabs][H][WH][E][2] partial filter gradients (slab = image group of the CTA)
+  int B, E, cls, nblk, pair_stride;
+  long long* prof;
+};
+
+// E1 (shared by dy and x): D1[h][slot,ri] (fp32) -> bf16 A operand [slot][h] at tAdst, 4 grid rows per store
+template <class C>
+__device__ __forceinline__ void epi_rows_to_cols(uint32_t tD, uint32_t tAdst, int g) {
+  constexpr int H = C::H, A2C = C::A2C;
+#pragma unroll
+  for (int hb = 0; hb < A2C; hb += 4) {
+    uint32_t v[4][8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (hb + i < H) tmem_ld8(tD + (hb + i) * 16 + 8 * g, v[i]);
+    tmem_wait_ld();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint32_t pk[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) pk[i] = (hb + i < H) ? pack_bf16(f32(v[i][2 * j]), f32(v[i][2 * j + 1])) : 0u;
+      tmem_st4(tAdst + (4 * g + j) * A2C + hb, pk);
+    }
+  }
+  tmem_wait_st();
+}
+
+template <int H, int W>
+__global__ void __launch_bounds__(kThreads, 1)
+fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x,
+                     const __grid_constant__ CUtensorMap tmap_dx, const BwdParams p) {
+  using C = Cfg<H, W>;
+  using SM = BwdSmem<H, W>;
+  constexpr int WH = C::WH, KWG = C::KWG, HG = C::HG, K2 = C::K2, A2C = C::A2C, UPK = K2 / 16;
+  constexpr int kADy = C::kACol, kAX = C::kACol + 128;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sDy = smem + SM::kDy;
+  uint8_t* sX = smem + SM::kX;
+  uint8_t* sOut = smem + SM::kOut;
+  float* sF = reinterpret_cast<float*>(smem + SM::kFilt);
+  uint8_t* sMat = smem + SM::kMat;
+  __shared__ uint64_t full_bar[2], empty_bar[2], dready_bar[6];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) uint8_t sDummy[8 * 16];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int cb = blockIdx.x % p.nblk;
+  const int pair0 = blockIdx.x / p.nblk;
+  const int c0 = cb * 64;
+  const int npairs = (p.B + 1) / 2;
+  const int ntiles = pair0 < npairs ? (npairs - pair0 + p.pair_stride - 1) / p.pair_stride : 0;
+  // slot -> kw (or -1): slots [0,KWG) and [4, 4+WH-KWG) are live
+  auto kw_of = [](int s) { return s < 4 ? (s < KWG ? s : -1) : (s - 4 < WH - KWG ? KWG + s - 4 : -1); };
+
+  // ---- one-time setup
+  if (warp == 8) tmem_alloc<512>(&tmem_base_s);
+  if (tid == 9 * 32) {
+    prefetch_tensormap(&tmap_dy);
+    prefetch_tensormap(&tmap_x);
+    prefetch_tensormap(&tmap_dx);
+    for (int s = 0; s < 2; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int k = 0; k < 6; ++k) mbar_init(&dready_bar[k], 1);
+    mbar_fence_init();
+    if (ntiles > 0) {   // prologue: first tile's dy and x
+      const int b0 = 2 * pair0;
+      const bool two = b0 + 1 < p.B;
+      const uint32_t bytes = (two ? 2u : 1u) * C::HW * 128u;
+      mbar_arrive_expect_tx(&full_bar[0], bytes);
+      tma_load_3d(sDy, &tmap_dy, &full_bar[0], c0, 0, b0);
+      if (two) tma_load_3d(sDy + C::kHalfStride, &tmap_dy, &full_bar[0], c0, 0, b0 + 1);
+      mbar_arrive_expect_tx(&full_bar[1], bytes);
+      tma_load_3d(sX, &tmap_x, &full_bar[1], c0, 0, b0);
+      if (two) tma_load_3d(sX + C::kHalfStride, &tmap_x, &full_bar[1], c0, 0, b0 + 1);
+    }
+  }
+  for (int i = tid; i < C::kMatBytes / 16; i += kThreads)
+    reinterpret_cast<uint4*>(sMat)[i] = reinterpret_cast<const uint4*>(g_mats<H, W>.w)[i];
+  {
+    // conj(filt) / (H*W) of this CTA's 64 channels: sF[c][slot][kh][re,im], channel stride padded
+    const float scale = 1.0f / static_cast<float>(H * W);
+    for (int i = tid; i < 64 * 8 * H; i += kThreads) {
+      const int cl = i & 63, rest = i >> 6, s = rest / H, kh = rest % H;
+      const int kw = kw_of(s);
+      float2 f = make_float2(0.f, 0.f);
+      if (kw >= 0 && c0 + cl < p.E)
+        f = __ldg(reinterpret_cast<const float2*>(p.filt) + (static_cast<size_t>(kh) * WH + kw) * p.E + c0 + cl);
+      *reinterpret_cast<float2*>(sF + cl * SM::kFiltStride + s * SM::kSlotF + kh * 2) = make_float2(f.x * scale, -f.y * scale);
+    }
+    for (int i = tid; i < 64 * 4; i += kThreads) sF[(i >> 2) * SM::kFiltStride + 8 * SM::kSlotF + (i & 3)] = 0.f;
+    if (SM::kSlotF > 2 * H)   // slot padding is read by the 16-byte filter loads: keep it finite
+      for (int i = tid; i < 64 * 8 * (SM::kSlotF - 2 * H); i += kThreads) {
+        constexpr int padn = SM::kSlotF - 2 * H > 0 ? SM::kSlotF - 2 * H : 1;
+        const int cl = i & 63, rest = i >> 6;
+        sF[cl * SM::kFiltStride + (rest / padn) * SM::kSlotF + 2 * H + rest % padn] = 0.f;
+      }
+    constexpr int per = (C::kHalfStride - C::HW * 128) / 16;
+    for (int i = tid; i < 4 * per; i += kThreads)   // rows past the image in the dy / x halves
+      reinterpret_cast<uint4*>(smem + (i / per) * C::kHalfStride + C::HW * 128)[i % per] = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tbase = tmem_base_s;
+
+  if (warp < 8) {
+    // =========================================================== epilogue warpgroups
+    setmaxnreg_inc<kEpiRegs>();
+    const int g = warp >> 2;
+    const int q = warp & 3;
+    const int m = q * 32 + lane;                               // TMEM lane: image (m >> 6), channel (m & 63)
+    const int c = c0 + (m & 63);
+    const bool cvalid = c < p.E;
+    const bool stamp = lane == 0 && q == 0;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    const uint32_t tD = tbase + lane_off + C::kDCol;
+    const uint32_t tADy = tbase + lane_off + kADy;
+    const uint32_t tAX = tbase + lane_off + kAX;
+    const uint32_t fthr = smem_u32(sF) + static_cast<uint32_t>(m & 63) * SM::kFiltStride * 4;
+
+    // filter-gradient accumulators: acc[hf][e][kh] for slot 4*hf + 2*g + e
+    float2 acc[2][2][H];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int e = 0; e < 2; ++e)
+#pragma unroll
+        for (int kh = 0; kh < H; ++kh) acc[a][e][kh] = make_float2(0.f, 0.f);
+
+    for (int it = 0; it < ntiles; ++it) {
+      const uint32_t par = it & 1;
+      const int b0 = 2 * (pair0 + it * p.pair_stride);
+      const bool two = b0 + 1 < p.B;
+      const bool mvalid = m < 64 || two;
+      // ---------------- rows(dy) -> A_dy ; rows(x) -> A_x
+      if (stamp) SB200_STAMP(g, it, 0);
+      mbar_wait(&dready_bar[0], par);
+      tc_fence_after_sync();
+      if (stamp) SB200_STAMP(g, it, 1);
+      epi_rows_to_cols<C>(tD, tADy, g);
+      tc_fence_before_sync();
+      named_bar_arrive(1, kBarCount);
+      if (stamp) SB200_STAMP(g, it, 2);
+      mbar_wait(&dready_bar[1], par);
+      tc_fence_after_sync();
+      if (stamp) SB200_STAMP(g, it, 3);
+      epi_rows_to_cols<C>(tD, tAX, g);
+      tc_fence_before_sync();
+      named_bar_arrive(2, kBarCount);
+      if (stamp) SB200_STAMP(g, it, 4);
+      // ---------------- cols: acc += conj(X) * DY ;  Z = conj(filt) * DY -> A_dy
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        mbar_wait(&dready_bar[2 + hf], par);
+        tc_fence_after_sync();
+        if (stamp) SB200_STAMP(g, it, 5 + 2 * hf);
+        constexpr int NU = 2 * UPK;                            // units: (e, half of the kh range)
+        const bool live0 = kw_of(4 * hf + 2 * g) >= 0, live1 = kw_of(4 * hf + 2 * g + 1) >= 0;
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          const int e = u / UPK, hk = u % UPK;
+          const bool live = e == 0 ? live0 : live1;
+          if (live) {
+            const int s = 4 * hf + 2 * g + e;
+            uint32_t vd[16], vx[16];
+            tmem_ld16(tD + (2 * g + e) * K2 + hk * 16, vd);
+            tmem_ld16(tD + 128 + (2 * g + e) * K2 + hk * 16, vx);
+            float4 f4[4];
+#pragma unroll
+            for (int qd = 0; qd < 4; ++qd)
+              asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                           : "=f"(f4[qd].x), "=f"(f4[qd].y), "=f"(f4[qd].z), "=f"(f4[qd].w)
+                           : "r"(fthr + static_cast<uint32_t>((s * SM::kSlotF + hk * 16 + qd * 4) * 4)));
+            tmem_wait_ld();
+            uint32_t z[8];
+#pragma unroll
+            for (int qq = 0; qq < 8; ++qq) {
+              const int kh = hk * 8 + qq;
+              if (kh < H) {
+                const float dr = f32(vd[2 * qq]), di = f32(vd[2 * qq + 1]);
+                const float xr = f32(vx[2 * qq]), xi = f32(vx[2 * qq + 1]);
+                const float fr = (qq & 1) ? f4[qq >> 1].z : f4[qq >> 1].x;   // already conj(filt)/(H*W)
+                const float fi = (qq & 1) ? f4[qq >> 1].w : f4[qq >> 1].y;
+                if (mvalid) {
+                  float2& a = acc[hf][e][kh < H ? kh : 0];
+                  a.x += xr * dr + xi * di;
+                  a.y += xr * di - xi * dr;
+                }
+                z[qq] = pack_bf16(fr * dr - fi * di, fr * di + fi * dr);
+              } else {
+                z[qq] = 0u;
+              }
+            }
+            tmem_st8(tADy + s * A2C + hk * 8, z);
+          }
+        }
+        tmem_wait_st();
+        tc_fence_before_sync();
+        named_bar_arrive(3 + hf, kBarCount);
+        if (stamp) SB200_STAMP(g, it, 6 + 2 * hf);
+      }
+      // ---------------- cols^-1: D3[slot][h,ri] -> A4[h][slot] (in the A_x region)
+      mbar_wait(&dready_bar[4], par);
+      tc_fence_after_sync();
+      if (stamp) SB200_STAMP(g, it, 9);
+#pragma unroll
+      for (int jp = 0; jp < 4; jp += 2) {
+        const int s0 = 4 * g + jp, s1 = s0 + 1;
+        const bool live0 = kw_of(s0) >= 0, live1 = kw_of(s1) >= 0;
+        uint32_t v0[K2], v1[K2];
+        if (live0) tmem_ld<K2>(tD + s0 * K2, v0);
+        if (live1) tmem_ld<K2>(tD + s1 * K2, v1);
+        tmem_wait_ld();
+#pragma unroll
+        for (int h = 0; h < H; ++h)
+          tmem_st2(tAX + h * 8 + s0, live0 ? pack_bf16(f32(v0[2 * h]), f32(v0[2 * h + 1])) : 0u,
+                   live1 ? pack_bf16(f32(v1[2 * h]), f32(v1[2 * h + 1])) : 0u);
+      }
+      tmem_wait_st();
+      tc_fence_before_sync();
+      named_bar_arrive(5, kBarCount);
+      if (stamp) SB200_STAMP(g, it, 10);
+      // ---------------- rows^-1: D4[h][w] -> bf16 -> swizzled smem tile -> TMA store of dx
+      if (tid == 0) tma_store_wait_read<0>();
+      mbar_wait(&dready_bar[5], par);
+      tc_fence_after_sync();
+      if (stamp) SB200_STAMP(g, it, 11);
+      {
+        const int mi = lane >> 3, rep = mi >> 1, up = mi & 1;
+        const int wtok = rep * 8 + (lane & 7);
+        const bool wvalid = wtok < W;
+        const uint32_t obase = smem_u32(sOut) + (q >> 1) * C::kHalfStride;
+        const uint32_t chunk0 = static_cast<uint32_t>(4 * (q & 1) + up);
+        const uint32_t dummy = smem_u32(sDummy) + (warp & 7) * 16;
+        auto stage4 = [&](auto gc) {
+          constexpr int G = decltype(gc)::value;
+          constexpr int h0 = G * HG;
+          uint32_t a[2][8], bq[2][8];
+          if (h0 < H) {
+            tmem_ld_16x256b_x2(tD + h0 * 16, a[0]);
+            tmem_ld_16x256b_x2(tD + (16u << 16) + h0 * 16, bq[0]);
+          }
+          named_bar_sync(7, kEpiThreads);                      // sOut free (thread 0 waited above)
+#pragma unroll
+          for (int i = 0; i < HG; ++i) {
+            if (h0 + i < H) {
+              tmem_wait_ld();
+              if (i + 1 < HG && h0 + i + 1 < H) {
+                tmem_ld_16x256b_x2(tD + (h0 + i + 1) * 16, a[(i + 1) & 1]);
+                tmem_ld_16x256b_x2(tD + (16u << 16) + (h0 + i + 1) * 16, bq[(i + 1) & 1]);
+              }
+              const int t = (h0 + i) * W + wtok;
+              const uint32_t row = obase + t * 128;
+              const uint32_t x7 = static_cast<uint32_t>(t & 7);
+              const uint32_t ad0 = wvalid ? row + ((chunk0 ^ x7) << 4) : dummy;
+              const uint32_t ad1 = wvalid ? row + (((chunk0 + 2) ^ x7) << 4) : dummy;
+              const uint32_t* u = a[i & 1];
+              const uint32_t* w2 = bq[i & 1];
+              stmatrix_x4_trans(ad0, pack_bf16(f32(u[0]), f32(u[1])), pack_bf16(f32(u[2]), f32(u[3])),
+                                pack_bf16(f32(u[4]), f32(u[5])), pack_bf16(f32(u[6]), f32(u[7])));
+              stmatrix_x4_trans(ad1, pack_bf16(f32(w2[0]), f32(w2[1])), pack_bf16(f32(w2[2]), f32(w2[3])),
+                                pack_bf16(f32(w2[4]), f32(w2[5])), pack_bf16(f32(w2[6]), f32(w2[7])));
+            }
+          }
+          tc_fence_before_sync();
+          if (it + 1 < ntiles) named_bar_arrive(6, kBarCount);   // D region free for the next tile
+          if (stamp) SB200_STAMP(G, it, 12);
+        };
+        if (g == 0) stage4(std::integral_constant<int, 0>{});
+        else stage4(std::integral_constant<int, 1>{});
+        fence_proxy_async_smem();
+        named_bar_sync(8, kEpiThreads);
+        if (tid == 0) {
+          tma_store_3d(&tmap_dx, sOut, c0, 0, b0);
+          if (two) tma_store_3d(&tmap_dx, sOut + C::kHalfStride, c0, 0, b0 + 1);
+          tma_store_commit();
+          if (it + 1 == ntiles) tma_store_wait_all<0>();
+        }
+      }
+      if (it + 1 == ntiles) {
+    // ---------------- all tiles done: add the two image halves of every channel, write this CTA's slab
+      {
+        float* scratch = reinterpret_cast<float*>(sDy);          // input tiles are dead by now
+        constexpr int kStride = 4 * H * 2 + 1;
+        float* mine = scratch + (g * 64 + (m & 63)) * kStride;
+        if (m >= 64) {
+#pragma unroll
+          for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+              for (int kh = 0; kh < H; ++kh) {
+                mine[((a * 2 + e) * H + kh) * 2] = acc[a][e][kh].x;
+                mine[((a * 2 + e) * H + kh) * 2 + 1] = acc[a][e][kh].y;
+              }
+        }
+        named_bar_sync(9, kEpiThreads);
+        if (m < 64 && cvalid && ntiles > 0) {
+          float2* slab = reinterpret_cast<float2*>(p.part) + static_cast<size_t>(pair0) * H * WH * p.E;
+#pragma unroll
+          for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int kw = kw_of(4 * a + 2 * g + e);
+              if (kw >= 0) {
+                const float wgt = ((kw == 0 || (W % 2 == 0 && kw == W / 2)) ? 1.0f : 2.0f) / static_cast<float>(H * W);
+#pragma unroll
+                for (int kh = 0; kh < H; ++kh) {
+                  const float sx = acc[a][e][kh].x + mine[((a * 2 + e) * H + kh) * 2];
+                  const float sy = acc[a][e][kh].y + mine[((a * 2 + e) * H + kh) * 2 + 1];
+                  slab[(static_cast<size_t>(kh) * WH + kw) * p.E + c] = make_float2(sx * wgt, sy * wgt);
+                }
+              }
+            }
+        }
+      }
+      }
+    }
+  } else {
+    setmaxnreg_dec<kAuxRegs>();
+    if (warp == 8) {
+      // ========================================================= MMA issuer
+      const uint32_t tD0 = tbase + C::kDCol, tADy0 = tbase + kADy, tAX0 = tbase + kAX;
+      const uint32_t id_row = umma_idesc_bf16(128, 16, 1, 0);
+      const uint32_t id_col = umma_idesc_bf16(128, K2, 0, 0);
+      const uint32_t id_irow = umma_idesc_bf16(128, 16, 0, 0);
+      const uint64_t b1 = umma_smem_desc(smem_u32(sMat + C::kOffB1), 128, 256, kSwzNone);
+      const uint64_t b4 = umma_smem_desc(smem_u32(sMat + C::kOffB4), 128, 256, kSwzNone);
+      const uint64_t b2 = umma_smem_desc(smem_u32(sMat + C::kOffB2), 128, (K2 / 8) * 128, kSwzNone);
+      const uint64_t b3 = umma_smem_desc(smem_u32(sMat + C::kOffB3), 128, (K2 / 8) * 128, kSwzNone);
+      const uint64_t a_dy0 = umma_smem_desc(smem_u32(sDy), C::kHalfStride, 1024, kSwz128);
+      const uint64_t a_x0 = umma_smem_desc(smem_u32(sX), C::kHalfStride, 1024, kSwz128);
+      for (int it = 0; it < ntiles; ++it) {
+        const uint32_t par = it & 1;
+        // keep the operand bases opaque per iteration: otherwise every "base + constant" of the ~110 MMAs is
+        // hoisted out of the loop and the issuing thread spills
+        uint64_t a_dy = a_dy0, a_x = a_x0;
+        uint32_t tD = tD0, tADy = tADy0, tAX = tAX0;
+        asm volatile("" : "+l"(a_dy), "+l"(a_x), "+r"(tD), "+r"(tADy), "+r"(tAX));
+        if (lane == 0) SB200_STAMP(2, it, 0);
+        mbar_wait(&full_bar[0], par);
+        if (it > 0) named_bar_sync(6, kBarCount);
+        tc_fence_after_sync();
+        if (lane == 0) SB200_STAMP(2, it, 1);
+        if (elect_one()) {
+#pragma unroll
+          for (int h = 0; h < H; ++h) umma_ss(tD + h * 16, a_dy + static_cast<uint64_t>(h * W * 8), b1, id_row, 0);
+          umma_commit(&empty_bar[0]);
+          umma_commit(&dready_bar[0]);
+        }
+        __syncwarp();
+        mbar_wait(&full_bar[1], par);
+        named_bar_sync(1, kBarCount);
+        tc_fence_after_sync();
+        if (lane == 0) SB200_STAMP(2, it, 2);
+        if (elect_one()) {
+#pragma unroll
+          for (int h = 0; h < H; ++h) umma_ss(tD + h * 16, a_x + static_cast<uint64_t>(h * W * 8), b1, id_row, 0);
+          umma_commit(&empty_bar[1]);
+          umma_commit(&dready_bar[1]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          named_bar_sync(2 + hf, kBarCount);
+          tc_fence_after_sync();
+          if (lane == 0) SB200_STAMP(2, it, 3 + hf);
+          if (elect_one()) {
+#pragma unroll
+            for (int sl = 0; sl < 4; ++sl) {
+              if (C::kw_of_slot(4 * hf + sl) >= 0) {
+#pragma unroll
+                for (int ks = 0; ks < K2 / 16; ++ks) {
+                  umma_ts(tD + sl * K2, tADy + (4 * hf + sl) * A2C + ks * 8, b2 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
+                  umma_ts(tD + 128 + sl * K2, tAX + (4 * hf + sl) * A2C + ks * 8, b2 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
+                }
+              }
+            }
+            umma_commit(&dready_bar[2 + hf]);
+          }
+          __syncwarp();
+        }
+        named_bar_sync(4, kBarCount);
+        tc_fence_after_sync();
+        if (lane == 0) SB200_STAMP(2, it, 5);
+        if (elect_one()) {
+#pragma unroll
+          for (int s = 0; s < 8; ++s) {
+            if (C::kw_of_slot(s) >= 0) {
+#pragma unroll
+              for (int ks = 0; ks < K2 / 16; ++ks)
+                umma_ts(tD + s * K2, tADy + s * A2C + ks * 8, b3 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
+            }
+          }
+          umma_commit(&dready_bar[4]);
+        }
+        __syncwarp();
+        named_bar_sync(5, kBarCount);
+        tc_fence_after_sync();
+        if (lane == 0) SB200_STAMP(2, it, 6);
+        if (elect_one()) {
+#pragma unroll
+          for (int h = 0; h < H; ++h) umma_ts(tD + h * 16, tAX + h * 8, b4, id_irow, 0);
+          umma_commit(&dready_bar[5]);
+        }
+        __syncwarp();
+        if (lane == 0) SB200_STAMP(2, it, 7);
+      }
+    } else if (warp == 9) {
+      // ========================================================= TMA producer + CLS pass-through
+      const int T = C::HW + p.cls;
+      for (int it = 0; it < ntiles; ++it) {
+        const int b0 = 2 * (pair0 + it * p.pair_stride);
+        const bool two = b0 + 1 < p.B;
+        const uint32_t bytes = (two ? 2u : 1u) * C::HW * 128u;
+        if (it > 0) {
+          mbar_wait(&empty_bar[0], (it - 1) & 1);
+          if (lane == 0) {
+            SB200_STAMP(3, it, 0);
+            mbar_arrive_expect_tx(&full_bar[0], bytes);
+            tma_load_3d(sDy, &tmap_dy, &full_bar[0], c0, 0, b0);
+            if (two) tma_load_3d(sDy + C::kHalfStride, &tmap_dy, &full_bar[0], c0, 0, b0 + 1);
+          }
+          mbar_wait(&empty_bar[1], (it - 1) & 1);
+          if (lane == 0) {
+            mbar_arrive_expect_tx(&full_bar[1], bytes);
+            tma_load_3d(sX, &tmap_x, &full_bar[1], c0, 0, b0);
+            if (two) tma_load_3d(sX + C::kHalfStride, &tmap_x, &full_bar[1], c0, 0, b0 + 1);
+          }
+        }
+        if (p.cls && lane < 16) {
+          const int img = b0 + (lane >> 3), cc = c0 + (lane & 7) * 8;
+          if (img < p.B && cc < p.E) {
+            const size_t off = static_cast<size_t>(img) * T * p.E + cc;
+            *reinterpret_cast<uint4*>(p.dx + off) = __ldg(reinterpret_cast<const uint4*>(p.dy + off));
+          }
+        }
+        __syncwarp();
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc<512>(tbase);
+}
+
+template <int H, int W>
+static int bwd_launch(const void* dy, const void* x, const float* filt, void* dx, float* dfilt, void* ws,
+                      size_t ws_bytes, int B, int E, int cls, cudaStream_t st) {
+  using C = Cfg<H, W>;
+  using SM = BwdSmem<H, W>;
+  auto kern = fftmix_tc_bwd_kernel<H, W>;
+  static bool configured = false;
+  if (!configured) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kBytes) != cudaSuccess)
+      return fail(SPECTRE_E_CUDA, "cudaFuncSetAttribute(tc bwd): %s", cudaGetErrorString(cudaGetLastError()));
+    configured = true;
+  }
+  BwdParams p;
+  plan_bwd_grid(B, E, &p.nblk, &p.pair_stride);
+  const size_t slab_floats = static_cast<size_t>(H) * C::WH * E * 2;
+  if (p.pair_stride > 1 && ws_bytes < slab_floats * sizeof(float) * p.pair_stride)
+    return fail(SPECTRE_E_WORKSPACE, "fftmix_tc_bwd: workspace %zu B < required %zu B", ws_bytes,
+                slab_floats * sizeof(float) * p.pair_stride);
+  CUtensorMap tmdy, tmx, tmdx;
+  if (int rc = make_token_map(&tmdy, dy, B, C::HW, C::HW + cls, E, cls)) return rc;
+  if (int rc = make_token_map(&tmx, x, B, C::HW, C::HW + cls, E, cls)) return rc;
+  if (int rc = make_token_map(&tmdx, dx, B, C::HW, C::HW + cls, E, cls)) return rc;
+  p.dy = static_cast<const __nv_bfloat16*>(dy);
+  p.filt = filt;
+  p.dx = static_cast<__nv_bfloat16*>(dx);
+  p.part = p.pair_stride > 1 ? static_cast<float*>(ws) : dfilt;
+  p.B = B; p.E = E; p.cls = cls;
+  p.prof = g_prof;
+  kern<<<p.nblk * p.pair_stride, kThreads, SM::kBytes, st>>>(tmdy, tmx, tmdx, p);
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "fftmix_tc_bwd launch: %s", cudaGetErrorString(err));
+  last_launch_count() = 1;
+  if (p.pair_stride > 1) {
+    launch_reduce_partials(p.part, dfilt, slab_floats, p.pair_stride, st);
+    err = cudaGetLastError();
+    if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "fftmix_tc_bwd reduce launch: %s", cudaGetErrorString(err));
+    last_launch_count() = 2;
+  }
+  return SPECTRE_OK;
+}
+
 }  // namespace tc
 
 // (H, W) grids with a tensor-core kernel; E must be a multiple of 8 (16-byte TMA strides)
@@ -633,6 +1155,20 @@ int fftmix_tc_fwd_dispatch(const void* x, const float* filt, void* y, int B, int
   SB200_TC_GRIDS(F)
 #undef F
   return fail(SPECTRE_E_GRID, "fftmix_tc: no tensor-core kernel for grid %dx%d", H, W);
+}
+
+int fftmix_tc_bwd_dispatch(const void* dy, const void* x, const float* filt, void* dx, float* dfilt, void* ws,
+                           size_t ws_bytes, int B, int H, int W, int E, int cls, cudaStream_t st) {
+#define F(h, w) if (H == h && W == w) return tc::bwd_launch<h, w>(dy, x, filt, dx, dfilt, ws, ws_bytes, B, E, cls, st);
+  SB200_TC_GRIDS(F)
+#undef F
+  return fail(SPECTRE_E_GRID, "fftmix_tc: no tensor-core kernel for grid %dx%d", H, W);
+}
+
+size_t fftmix_tc_bwd_workspace(int B, int H, int W, int E) {
+  int nblk, stride;
+  tc::plan_bwd_grid(B, E, &nblk, &stride);
+  return stride > 1 ? static_cast<size_t>(stride) * H * (W / 2 + 1) * E * 2 * sizeof(float) : 0;
 }
 
 }  // namespace sb200
