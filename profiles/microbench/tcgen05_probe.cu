@@ -257,7 +257,7 @@ mma_probe_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* __res
 // ------------------------------------------------------------------ T5: unrolled issue rate (what the real kernel does)
 // One tile's worth of MMAs of the 14x14 mixer: 14 SS (N=16) + 16 TS (N=32) + 16 TS + 14 TS (N=16),
 // all descriptors compile-time offsets from registers, fully unrolled.  Garbage operands; timing only.
-__global__ void __launch_bounds__(128, 1) mma_unrolled_kernel(long long* cyc, int reps) {
+__global__ void __launch_bounds__(128, 1) mma_unrolled_kernel(long long* cyc, int reps, int row_stride16) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ uint32_t tbase_s;
@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(128, 1) mma_unrolled_kernel(long long* cyc, in
     for (int r = 0; r < reps; ++r) {
       const long long t0 = clock64();
 #pragma unroll
-      for (int h = 0; h < 14; ++h) umma_ss(tb + h * 16, a0 + (uint64_t)(h * 2048 / 16), b1, id_row, 0);
+      for (int h = 0; h < 14; ++h) umma_ss(tb + h * 16, a0 + (uint64_t)(h * row_stride16), b1, id_row, 0);
       const long long t1 = clock64();
 #pragma unroll
       for (int kw = 0; kw < 8; ++kw) {
@@ -494,8 +494,9 @@ int main(int argc, char** argv) {
   if (want("t5")) {
     long long* dc; CK(cudaMalloc(&dc, 64));
     CK(cudaFuncSetAttribute(mma_unrolled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
-    for (int reps : {1, 16}) {
-      mma_unrolled_kernel<<<1, 128, 65536>>>(dc, reps);
+    for (int rs : {128, 112}) for (int reps : {1, 16}) {
+      printf("row stride %d B: ", rs * 16);
+      mma_unrolled_kernel<<<1, 128, 65536>>>(dc, reps, rs);
       cudaError_t e = cudaDeviceSynchronize();
       if (e != cudaSuccess) { printf("[T5] CUDA ERROR %s\n", cudaGetErrorString(e)); return 1; }
       long long h[8]; CK(cudaMemcpy(h, dc, 48, cudaMemcpyDeviceToHost));

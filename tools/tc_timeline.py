@@ -55,4 +55,5 @@ for who in range(WHO):
         row = p[who, t]
         vals = [int(v) - t0 if int(v) else None for v in row[:13]]
         if any(v is not None for v in vals):
-            print(f"{names[who]:7s} tile{t}: " + " ".join("-" if v is None else str(v) for v in vals))
+            d = [vals[i] - vals[i - 1] if i and vals[i] is not None and vals[i - 1] is not None else 0 for i in range(len(vals))]
+            print(f"{names[who]:7s} tile{t}: start {vals[0]} deltas " + " ".join(str(x) for x in d[1:]))

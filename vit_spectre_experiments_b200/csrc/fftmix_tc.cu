@@ -229,9 +229,8 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
       const bool ok = kw < WH && cvalid;
 #pragma unroll
       for (int kh = 0; kh < H; ++kh) {
-        float2 f = make_float2(0.f, 0.f);
-        if (ok) f = __ldg(fp + (static_cast<size_t>(kh) * WH + kw) * p.E);
-        Fld[j][kh] = make_float2(f.x * scale, f.y * scale);
+        const float2 f = __ldg(fp + (ok ? (static_cast<size_t>(kh) * WH + kw) * p.E : 0));   // branch-free
+        Fld[j][kh] = ok ? make_float2(f.x * scale, f.y * scale) : make_float2(0.f, 0.f);
       }
     }
   }
@@ -694,6 +693,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) uint8_t sDummy[8 * 16];
 
+  const long long t_start = clock64();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int cb = blockIdx.x % p.nblk;
   const int pair0 = blockIdx.x / p.nblk;
@@ -705,6 +705,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
 
   // ---- one-time setup
   if (warp == 8) tmem_alloc<512>(&tmem_base_s);
+  if (tid == 8 * 32) SB200_STAMP(5, 0, 0);
   if (tid == 9 * 32) {
     prefetch_tensormap(&tmap_dy);
     prefetch_tensormap(&tmap_x);
@@ -723,20 +724,39 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
       tma_load_3d(sX, &tmap_x, &full_bar[1], c0, 0, b0);
       if (two) tma_load_3d(sX + C::kHalfStride, &tmap_x, &full_bar[1], c0, 0, b0 + 1);
     }
+    SB200_STAMP(5, 0, 1);
   }
   for (int i = tid; i < C::kMatBytes / 16; i += kThreads)
     reinterpret_cast<uint4*>(sMat)[i] = reinterpret_cast<const uint4*>(g_mats<H, W>.w)[i];
+  if (tid == 0) SB200_STAMP(5, 0, 2);
   {
-    // conj(filt) / (H*W) of this CTA's 64 channels: sF[c][slot][kh][re,im], channel stride padded
+    // conj(filt) / (H*W) of this CTA's 64 channels: sF[c][slot][kh][re,im], channel stride padded.
+    // All global loads are issued before the first shared-memory store (memory-level parallelism:
+    // a load->store loop would serialise ~20 DRAM round trips per thread).
     const float scale = 1.0f / static_cast<float>(H * W);
-    for (int i = tid; i < 64 * 8 * H; i += kThreads) {
+    constexpr int kIters = (64 * 8 * H + kThreads - 1) / kThreads;
+    float2 fv[kIters];
+#pragma unroll
+    for (int k = 0; k < kIters; ++k) {
+      const int i = tid + k * kThreads;
       const int cl = i & 63, rest = i >> 6, s = rest / H, kh = rest % H;
-      const int kw = kw_of(s);
-      float2 f = make_float2(0.f, 0.f);
-      if (kw >= 0 && c0 + cl < p.E)
-        f = __ldg(reinterpret_cast<const float2*>(p.filt) + (static_cast<size_t>(kh) * WH + kw) * p.E + c0 + cl);
-      *reinterpret_cast<float2*>(sF + cl * SM::kFiltStride + s * SM::kSlotF + kh * 2) = make_float2(f.x * scale, -f.y * scale);
+      const int kw = i < 64 * 8 * H ? kw_of(s) : -1;
+      // branch-free (clamped address + select) so the loads issue back to back
+      const bool ok = kw >= 0 && c0 + cl < p.E;
+      const size_t off = ok ? (static_cast<size_t>(kh) * WH + kw) * p.E + c0 + cl : 0;
+      const float2 f = __ldg(reinterpret_cast<const float2*>(p.filt) + off);
+      fv[k] = ok ? f : make_float2(0.f, 0.f);
     }
+    if (tid == 0) SB200_STAMP(5, 0, 3);
+#pragma unroll
+    for (int k = 0; k < kIters; ++k) {
+      const int i = tid + k * kThreads;
+      const int cl = i & 63, rest = i >> 6, s = rest / H, kh = rest % H;
+      if (i < 64 * 8 * H)
+        *reinterpret_cast<float2*>(sF + cl * SM::kFiltStride + s * SM::kSlotF + kh * 2) =
+            make_float2(fv[k].x * scale, -fv[k].y * scale);
+    }
+    if (tid == 0) SB200_STAMP(5, 0, 4);
     for (int i = tid; i < 64 * 4; i += kThreads) sF[(i >> 2) * SM::kFiltStride + 8 * SM::kSlotF + (i & 3)] = 0.f;
     if (SM::kSlotF > 2 * H)   // slot padding is read by the 16-byte filter loads: keep it finite
       for (int i = tid; i < 64 * 8 * (SM::kSlotF - 2 * H); i += kThreads) {
@@ -750,9 +770,11 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
   }
   fence_proxy_async_smem();
   tc_fence_before_sync();
+  if (tid == 0) SB200_STAMP(5, 0, 5);
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tbase = tmem_base_s;
+  if (tid == 0 && p.prof && blockIdx.x == 0) { p.prof[14] = t_start; p.prof[15] = clock64(); }
 
   if (warp < 8) {
     // =========================================================== epilogue warpgroups
