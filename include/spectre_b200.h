@@ -78,6 +78,39 @@ int spectre_dwtmix_bwd(const void* dy, const void* x, const float* w,
                        int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);
 size_t spectre_dwtmix_bwd_workspace_bytes(int B, int H, int W, int E);
 
+
+/* ---------------------------------------------------------------------------------------------------
+ * Fused row-wise tail of the layers around the mixer:
+ *
+ *     out = dropout( act( LayerNorm(in0 + in1) * gamma + beta ) + adaptive_avg_pool(skip) )
+ *
+ * replaces, in one pass per direction,
+ *   spectre_vit/models/spectre/spectre.py:66      x = self.norm1(self.mix_layer(x)) + x     (in0 = mix, skip = x)
+ *   spectre_vit/models/spectre/layers.py:95-101   local_head(x) + avg_pool(x)               (in0 = Linear(x), act = GELU, skip = x)
+ *   spectre_vit/models/spectre/spectre.py:67      self.norm2(x + self._ff_block(x))         (in0 = x, in1 = ff)
+ * rows x N row-major, fp32 arithmetic.  in0 is float32 or bfloat16 (in0_dtype); in1 / skip / out are
+ * float32; out_bf16 (optional) receives a bfloat16 copy of out for the next bf16 consumer (GEMM / mixer).
+ * skip is [rows, Ns] and is pooled to N with torch.nn.AdaptiveAvgPool1d semantics (Ns == N: identity).
+ * Dropout is counter-based: element (row, col) is kept iff hash(seed, row*N+col) >= drop_p * 2^32, so
+ * the backward recomputes the mask from (seed, drop_p); drop_p = 0 disables it.
+ * Backward: dout (+ optional dout_bf16, the gradient that arrived through the bf16 copy) ->
+ *   d_in0 (in0_dtype, optional), d_in1 (float32, optional; same values), d_skip [rows, Ns], dgamma, dbeta.
+ * mean / rstd [rows] are written by forward and read by backward.  workspace >=
+ * spectre_norm_act_bwd_workspace_bytes(rows, N) bytes (per-CTA gamma/beta partials, summed in a fixed order). */
+typedef struct spectre_norm_act_t {
+  const void* in0; const float* in1; const float* gamma; const float* beta; const float* skip;
+  float* out; void* out_bf16; float* mean; float* rstd;
+  const float* dout; const void* dout_bf16;
+  void* d_in0; float* d_in1; float* d_skip; float* dgamma; float* dbeta;
+  void* workspace; size_t workspace_bytes;
+  long long rows; int N; int Ns; int in0_dtype; int act /* 0 identity, 1 GELU(erf) */;
+  float eps; float drop_p; unsigned long long seed;
+} spectre_norm_act_t;
+
+int spectre_norm_act_fwd(const spectre_norm_act_t* desc, void* stream);
+int spectre_norm_act_bwd(const spectre_norm_act_t* desc, void* stream);
+size_t spectre_norm_act_bwd_workspace_bytes(long long rows, int N);
+
 /* 1 if (H, W) has a compiled FFT-mixer kernel, else 0. */
 int spectre_fftmix_supported(int H, int W);
 

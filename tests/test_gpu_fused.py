@@ -1,0 +1,123 @@
+"""Parity of the fused row-wise tail kernels (C ABI ``spectre_norm_act_*``)
+against the stock torch composition they replace (``spectre.py:65-73``, ``layers.py:95-101``).  `-m gpu` only."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_err(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+def ref_norm_act(in0, gamma, beta, in1, skip, act, eps=1e-5):
+    z = in0.float() if in1 is None else in0.float() + in1
+    u = F.layer_norm(z, (z.shape[-1],), gamma, beta, eps)
+    if act == "gelu":
+        u = F.gelu(u)
+    if skip is not None:
+        N = z.shape[-1]
+        u = u + (skip if skip.shape[-1] == N else F.adaptive_avg_pool1d(skip, N))
+    return u
+
+
+CASES = [
+    # rows-shape, N, Ns, in0 dtype, in1, act      which line of the reference layer
+    ((6, 197), 384, 384, torch.bfloat16, False, "none"),    # x1 = LN1(mix) + x            (spectre.py:66)
+    ((6, 197), 1536, 384, torch.bfloat16, False, "gelu"),   # GELU(LN(h1)) + pool_up(x1)    (layers.py:95-101)
+    ((6, 197), 384, 1536, torch.bfloat16, False, "gelu"),   # GELU(LN(h2)) + pool_down(a1)
+    ((6, 197), 384, None, torch.float32, True, "none"),     # x2 = LN2(x1 + ff)            (spectre.py:67)
+    ((3, 65), 768, 512, torch.float32, False, "gelu"),      # C1 widths: general adaptive pool 512 -> 768
+    ((3, 65), 512, 768, torch.float32, False, "gelu"),      #            and 768 -> 512
+    ((5, 50), 48, 48, torch.float32, False, "none"),        # C2 width 48 (single partial warp)
+    ((5, 50), 256, 48, torch.float32, False, "gelu"),       # 48 -> 256 (general)
+    ((2, 197), 3072, 768, torch.bfloat16, False, "gelu"),   # ViT-B widths
+    ((2, 197), 768, 3072, torch.bfloat16, False, "gelu"),
+]
+
+
+@pytest.mark.parametrize("shape,N,Ns,dtype,has_in1,act", CASES)
+def test_norm_act_fwd_bwd(cuda_device, shape, N, Ns, dtype, has_in1, act):
+    from vit_spectre_experiments_b200.fused import norm_act
+
+    g = torch.Generator().manual_seed(N * 7 + (Ns or 0))
+    in0 = torch.randn(*shape, N, generator=g).to(dtype)
+    in1 = torch.randn(*shape, N, generator=g) if has_in1 else None
+    skip = torch.randn(*shape, Ns, generator=g) if Ns else None
+    gamma = 1 + 0.3 * torch.randn(N, generator=g)
+    beta = 0.2 * torch.randn(N, generator=g)
+    dout = torch.randn(*shape, N, generator=g)
+    dout_b = torch.randn(*shape, N, generator=g).to(torch.bfloat16)
+
+    def leaf(t):
+        return None if t is None else t.clone().requires_grad_(True)
+
+    # reference (fp32 torch on the same, bf16-rounded, inputs)
+    r = [leaf(in0.float()), leaf(gamma), leaf(beta), leaf(in1), leaf(skip)]
+    y_ref = ref_norm_act(r[0], r[1], r[2], r[3], r[4], act)
+    (y_ref * dout).sum().backward() if dtype == torch.float32 else (y_ref * (dout + dout_b.float())).sum().backward()
+
+    d = [None if t is None else t.to(cuda_device) for t in (in0, gamma, beta, in1, skip)]
+    d = [leaf(t) for t in d]
+    want_twin = dtype == torch.bfloat16
+    y, yb = norm_act(d[0], d[1], d[2], in1=d[3], skip=d[4], act=act, want_bf16=want_twin)
+    assert y.dtype == torch.float32 and rel_err(y, y_ref) <= 2e-6
+    if want_twin:
+        assert yb.dtype == torch.bfloat16 and rel_err(yb, y_ref.to(torch.bfloat16)) <= 1e-2
+        torch.autograd.backward([y, yb], [dout.to(cuda_device), dout_b.to(cuda_device)])
+    else:
+        assert yb is None
+        y.backward(dout.to(cuda_device))
+    tol_in0 = 1e-5 if dtype == torch.float32 else 1e-2       # d_in0 is rounded to in0's dtype
+    assert d[0].grad.dtype == dtype and rel_err(d[0].grad, r[0].grad) <= tol_in0
+    assert rel_err(d[1].grad, r[1].grad) <= 2e-5 and rel_err(d[2].grad, r[2].grad) <= 2e-5
+    if has_in1:
+        assert rel_err(d[3].grad, r[3].grad) <= 1e-5
+    if Ns:
+        assert rel_err(d[4].grad, r[4].grad) <= 1e-5
+
+
+def test_norm_act_dropout_is_consistent(cuda_device):
+    """Counter-based dropout: forward and backward use the same mask; keep-rate ~ 1 - p; scaling 1/(1-p)."""
+    from vit_spectre_experiments_b200.fused import norm_act
+
+    x = torch.randn(64, 197, 384, device=cuda_device).requires_grad_(True)
+    gamma, beta = torch.ones(384, device=cuda_device), torch.zeros(384, device=cuda_device)
+    y0, _ = norm_act(x, gamma, beta)
+    y, _ = norm_act(x, gamma, beta, drop_p=0.25, seed=1234)
+    kept = y != 0
+    assert abs(kept.float().mean().item() - 0.75) < 5e-3
+    assert torch.allclose(y[kept], y0[kept] / 0.75, rtol=1e-6, atol=1e-6)
+    y2, _ = norm_act(x, gamma, beta, drop_p=0.25, seed=1234)
+    assert torch.equal(y, y2)
+    # gradient flows only through kept elements: d/dx of sum(y * w) with w = 1 on dropped positions is 0
+    (y * (~kept).float()).sum().backward()
+    assert x.grad.abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("autocast", [False, True])
+def test_encoder_layer_fused_matches_torch(cuda_device, autocast):
+    """Whole SpectreEncoderLayer: fused path == stock torch composition (same parameters, same input)."""
+    from vit_spectre_experiments_b200 import SpectreEncoderLayer
+
+    torch.manual_seed(3)
+    kw = dict(seq_length=65, d_model=128, nhead=4, dim_feedforward=256, dropout=0.0, activation="gelu", mixer="fft",
+              grid=(8, 8))
+    a = SpectreEncoderLayer(**kw, fused=True).to(cuda_device)
+    b = SpectreEncoderLayer(**kw, fused=False).to(cuda_device)
+    b.load_state_dict(a.state_dict())
+    x = torch.randn(16, 65, 128, device=cuda_device)
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+        ya, yb = a(xa), b(xb)
+    assert a.use_fused(x) and not b.use_fused(x)
+    w = torch.randn_like(ya)
+    (ya * w).sum().backward()
+    (yb * w).sum().backward()
+    tol = 2e-2 if autocast else 2e-5
+    assert rel_err(ya, yb) <= tol and rel_err(xa.grad, xb.grad) <= tol
+    pa, pb = dict(a.named_parameters()), dict(b.named_parameters())
+    for k in pa:
+        assert rel_err(pa[k].grad, pb[k].grad) <= (5e-2 if autocast else 1e-4), k

@@ -20,11 +20,29 @@ EXPORTED_SYMBOLS = (
     "spectre_dwtmix_fwd",
     "spectre_dwtmix_bwd",
     "spectre_dwtmix_bwd_workspace_bytes",
+    "spectre_norm_act_fwd",
+    "spectre_norm_act_bwd",
+    "spectre_norm_act_bwd_workspace_bytes",
     "spectre_fftmix_supported",
     "spectre_last_launch_count",
     "spectre_last_error",
     "spectre_version",
 )
+
+class NormActDesc(ctypes.Structure):
+    """``spectre_norm_act_t`` of include/spectre_b200.h (field order matters)."""
+
+    _fields_ = [
+        ("in0", ctypes.c_void_p), ("in1", ctypes.c_void_p), ("gamma", ctypes.c_void_p), ("beta", ctypes.c_void_p),
+        ("skip", ctypes.c_void_p), ("out", ctypes.c_void_p), ("out_bf16", ctypes.c_void_p), ("mean", ctypes.c_void_p),
+        ("rstd", ctypes.c_void_p), ("dout", ctypes.c_void_p), ("dout_bf16", ctypes.c_void_p),
+        ("d_in0", ctypes.c_void_p), ("d_in1", ctypes.c_void_p), ("d_skip", ctypes.c_void_p),
+        ("dgamma", ctypes.c_void_p), ("dbeta", ctypes.c_void_p), ("workspace", ctypes.c_void_p),
+        ("workspace_bytes", ctypes.c_size_t), ("rows", ctypes.c_longlong), ("N", ctypes.c_int), ("Ns", ctypes.c_int),
+        ("in0_dtype", ctypes.c_int), ("act", ctypes.c_int), ("eps", ctypes.c_float), ("drop_p", ctypes.c_float),
+        ("seed", ctypes.c_ulonglong),
+    ]
+
 
 _lock = threading.Lock()
 _lib = None
@@ -57,6 +75,12 @@ def load() -> ctypes.CDLL:
         lib.spectre_dwtmix_bwd.restype = _i
         lib.spectre_dwtmix_bwd_workspace_bytes.argtypes = [_i, _i, _i, _i]
         lib.spectre_dwtmix_bwd_workspace_bytes.restype = _sz
+        lib.spectre_norm_act_fwd.argtypes = [ctypes.POINTER(NormActDesc), _p]
+        lib.spectre_norm_act_fwd.restype = _i
+        lib.spectre_norm_act_bwd.argtypes = [ctypes.POINTER(NormActDesc), _p]
+        lib.spectre_norm_act_bwd.restype = _i
+        lib.spectre_norm_act_bwd_workspace_bytes.argtypes = [ctypes.c_longlong, _i]
+        lib.spectre_norm_act_bwd_workspace_bytes.restype = _sz
         lib.spectre_fftmix_supported.argtypes = [_i, _i]
         lib.spectre_fftmix_supported.restype = _i
         lib.spectre_last_launch_count.argtypes = []

@@ -18,6 +18,8 @@ them "next"); the hand-written kernels sit behind ``mix_layer`` only.
 from __future__ import annotations
 
 import copy
+import itertools
+import os
 
 import torch
 import torch.nn as nn
@@ -26,6 +28,16 @@ import torch.nn.functional as F
 from .mixers import HaarDWTMix, SpectralFilterMix
 
 MIXERS = ("permut", "fft", "dwt")
+
+# SB200_FUSED=0 keeps the stock torch composition of LayerNorm / GELU / pool / add around the mixer and
+# the GEMMs on CUDA too (A/B measurements); default: the fused norm_act kernels (fused.py).
+_FUSED_DEFAULT = os.environ.get("SB200_FUSED", "1") != "0"
+_seed_counter = itertools.count(1)
+
+
+def _dropout_seed() -> int:
+    """Per-call seed of the counter-based dropout in the fused tail (deterministic under manual_seed)."""
+    return (torch.initial_seed() * 0x9E3779B1 + next(_seed_counter) * 0x85EBCA77) & 0x7FFFFFFFFFFFFFFF
 
 
 class SpectreLinear(nn.Module):
@@ -83,10 +95,14 @@ def build_mixer(mixer: str, d_model: int, seq_length: int, nhead: int, grid=None
 
 
 class SpectreEncoderLayer(nn.Module):
-    """``x = LN1(mix(x)) + x ; x = LN2(x + FF(x))`` (spectre.py:65-73)."""
+    """``x = LN1(mix(x)) + x ; x = LN2(x + FF(x))`` (spectre.py:65-73).
+
+    On CUDA the row-wise pieces around the mixer and the two GEMMs run as fused ``norm_act`` kernels
+    (``fused.py``); parameters, ``state_dict`` keys and results are those
+    of the torch composition below, which stays the CPU / reference path."""
 
     def __init__(self, seq_length, d_model, nhead, dim_feedforward, dropout, activation, *, mixer="permut",
-                 grid=None):
+                 grid=None, fused=None):
         super().__init__()
         self.mix_layer = build_mixer(mixer, d_model, seq_length, nhead, grid)
         self.linear1 = SpectreLinear(d_model, dim_feedforward)
@@ -96,13 +112,43 @@ class SpectreEncoderLayer(nn.Module):
         self.dropout1 = nn.Dropout(dropout)
         self.dropout2 = nn.Dropout(dropout)
         self.activation = getattr(F, activation) if isinstance(activation, str) else activation
+        self.fused = _FUSED_DEFAULT if fused is None else bool(fused)
+        self._fusable = d_model % 8 == 0 and dim_feedforward % 8 == 0
 
     def _ff_block(self, x: torch.Tensor) -> torch.Tensor:
         return self.dropout2(self.linear3(self.dropout1(self.linear1(x))))
 
+    def use_fused(self, x: torch.Tensor) -> bool:
+        if not (self.fused and self._fusable and x.is_cuda and x.dtype == torch.float32):
+            return False
+        return not torch.is_autocast_enabled() or torch.get_autocast_dtype("cuda") == torch.bfloat16
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.use_fused(x):
+            return self.forward_fused(x, None)[0]
         x = self.norm1(self.mix_layer(x)) + x
         return self.norm2(x + self._ff_block(x))
+
+    def forward_fused(self, x: torch.Tensor, x_bf16):
+        """Same arithmetic through the fused kernels.  ``x_bf16`` is an optional bf16 twin of ``x`` (written
+        by the previous layer's last kernel) that feeds the bf16 mixer without a cast pass; returns
+        ``(x2_float32, x2_bfloat16 | None)``."""
+        from .fused import norm_act
+
+        twin = torch.is_autocast_enabled()
+        m = self.mix_layer(x_bf16 if (twin and x_bf16 is not None) else x)
+        x1, x1b = norm_act(m, self.norm1.weight, self.norm1.bias, skip=x, eps=self.norm1.eps, want_bf16=twin)
+        lin1, ln1 = self.linear1.local_head[0], self.linear1.local_head[1]
+        lin3, ln3 = self.linear3.local_head[0], self.linear3.local_head[1]
+        p1 = self.dropout1.p if self.training else 0.0
+        p2 = self.dropout2.p if self.training else 0.0
+        h1 = F.linear(x1b if x1b is not None else x1, lin1.weight, lin1.bias)
+        a1, a1b = norm_act(h1, ln1.weight, ln1.bias, skip=x1, eps=ln1.eps, act="gelu", drop_p=p1,
+                           seed=_dropout_seed() if p1 > 0 else 0, want_bf16=twin)
+        h2 = F.linear(a1b if a1b is not None else a1, lin3.weight, lin3.bias)
+        ff, _ = norm_act(h2, ln3.weight, ln3.bias, skip=a1, eps=ln3.eps, act="gelu", drop_p=p2,
+                         seed=_dropout_seed() if p2 > 0 else 0)
+        return norm_act(x1, self.norm2.weight, self.norm2.bias, in1=ff, eps=self.norm2.eps, want_bf16=twin)
 
 
 class SpectreEncoder(nn.Module):
@@ -117,8 +163,13 @@ class SpectreEncoder(nn.Module):
 
     def forward(self, src: torch.Tensor) -> torch.Tensor:
         out = src
-        for layer in self.layers:
-            out = layer(out)
+        if all(isinstance(l, SpectreEncoderLayer) and l.use_fused(src) for l in self.layers):
+            twin = None   # bf16 copy of `out`, handed from layer to layer under autocast
+            for layer in self.layers:
+                out, twin = layer.forward_fused(out, twin)
+        else:
+            for layer in self.layers:
+                out = layer(out)
         if self.norm is not None:
             out = self.norm(out)
         return out + src
