@@ -250,6 +250,9 @@ def main():
         except Exception:
             pass
         for name, (n, mean_ms, meta) in ksum.items():
+            if len(meta) != 5:      # row-wise tails (norm_act_*): rows, N, element size -- time only
+                kernels[name] = {"launches": n, "mean_ms": round(mean_ms, 4)}
+                continue
             Bk, Hk, Wk, Ek, sz = meta
             nbytes = (3 if name.endswith("bwd") else 2) * Bk * T * Ek * sz + (2 if name.endswith("bwd") else 1) * F
             kernels[name] = {"launches": n, "mean_ms": round(mean_ms, 4), "algo_bytes": nbytes,
