@@ -88,22 +88,23 @@ size_t spectre_dwtmix_bwd_workspace_bytes(int B, int H, int W, int E);
  *   spectre_vit/models/spectre/spectre.py:66      x = self.norm1(self.mix_layer(x)) + x     (in0 = mix, skip = x)
  *   spectre_vit/models/spectre/layers.py:95-101   local_head(x) + avg_pool(x)               (in0 = Linear(x), act = GELU, skip = x)
  *   spectre_vit/models/spectre/spectre.py:67      self.norm2(x + self._ff_block(x))         (in0 = x, in1 = ff)
- * rows x N row-major, fp32 arithmetic.  in0 is float32 or bfloat16 (in0_dtype); in1 / skip / out are
- * float32; out_bf16 (optional) receives a bfloat16 copy of out for the next bf16 consumer (GEMM / mixer).
+ * rows x N row-major.  Every activation tensor of a call (in0, in1, skip, out, dout, d_in0, d_skip) has the
+ * element type act_dtype (float32, or bfloat16 for the bf16 training stream); gamma / beta, the row
+ * statistics and all arithmetic are float32.
  * skip is [rows, Ns] and is pooled to N with torch.nn.AdaptiveAvgPool1d semantics (Ns == N: identity).
- * Dropout is counter-based: element (row, col) is kept iff hash(seed, row*N+col) >= drop_p * 2^32, so
+ * Dropout is counter-based: element (row, col) is kept iff hash(seed, row, col) >= drop_p * 2^32, so
  * the backward recomputes the mask from (seed, drop_p); drop_p = 0 disables it.
- * Backward: dout (+ optional dout_bf16, the gradient that arrived through the bf16 copy) ->
- *   d_in0 (in0_dtype, optional), d_in1 (float32, optional; same values), d_skip [rows, Ns], dgamma, dbeta.
+ * Backward: dout -> d_in0 (also the gradient of in1: the same values), d_skip [rows, Ns] (non-null iff the
+ * forward had a skip; `skip` itself is not read), dgamma, dbeta (fully overwritten).
  * mean / rstd [rows] are written by forward and read by backward.  workspace >=
  * spectre_norm_act_bwd_workspace_bytes(rows, N) bytes (per-CTA gamma/beta partials, summed in a fixed order). */
 typedef struct spectre_norm_act_t {
-  const void* in0; const float* in1; const float* gamma; const float* beta; const float* skip;
-  float* out; void* out_bf16; float* mean; float* rstd;
-  const float* dout; const void* dout_bf16;
-  void* d_in0; float* d_in1; float* d_skip; float* dgamma; float* dbeta;
+  const void* in0; const void* in1; const float* gamma; const float* beta; const void* skip;
+  void* out; float* mean; float* rstd;
+  const void* dout;
+  void* d_in0; void* d_skip; float* dgamma; float* dbeta;
   void* workspace; size_t workspace_bytes;
-  long long rows; int N; int Ns; int in0_dtype; int act /* 0 identity, 1 GELU(erf) */;
+  long long rows; int N; int Ns; int act_dtype; int act /* 0 identity, 1 GELU(erf) */;
   float eps; float drop_p; unsigned long long seed;
 } spectre_norm_act_t;
 

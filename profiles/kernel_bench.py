@@ -55,7 +55,7 @@ def time_ms(fn, iters, flush):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=20)
-    ap.add_argument("--only", default="")
+    ap.add_argument("--only", default="", help="fft | dwt | na")
     ap.add_argument("--match", default="", help="substring of the shape name")
     args = ap.parse_args()
     lib = _lib.load()
@@ -94,6 +94,67 @@ def main():
                 "algo_MB": round(nbytes / 1e6, 2), "GBps_median": round(nbytes / med / 1e6, 1),
                 "GBps_best": round(nbytes / best / 1e6, 1), "frac_of_measured_peak": round(nbytes / med / 1e6 / PEAK, 3),
                 "workspace_MB": round(nws / 1e6, 2),
+            }), flush=True)
+
+    if args.only in ("", "na"):
+        norm_act_bench(args, dev, flush)
+
+
+# the four row-wise tails of one C4 encoder layer (rows = 256 * 197) + C3 widths
+NA_SHAPES = [
+    # name, rows, N, Ns, has_in1, act, drop_p, dtype
+    ("C4 LN1(mix)+x N384", 256 * 197, 384, 384, False, "none", 0.0, torch.bfloat16),
+    ("C4 GELU(LN(h1))+up N1536", 256 * 197, 1536, 384, False, "gelu", 0.001, torch.bfloat16),
+    ("C4 GELU(LN(h2))+down N384", 256 * 197, 384, 1536, False, "gelu", 0.001, torch.bfloat16),
+    ("C4 LN2(x1+ff) N384", 256 * 197, 384, None, True, "none", 0.0, torch.bfloat16),
+    ("C4 GELU(LN(h1))+up N1536 f32", 256 * 197, 1536, 384, False, "gelu", 0.001, torch.float32),
+    ("C3 GELU(LN(h1))+general 512->768", 1024 * 65, 768, 512, False, "gelu", 0.001, torch.bfloat16),
+]
+
+
+def norm_act_bench(args, dev, flush):
+    from vit_spectre_experiments_b200.fused import norm_act
+
+    for name, rows, N, Ns, has_in1, act, p, dt in NA_SHAPES:
+        if args.match and args.match not in name:
+            continue
+        s = 4 if dt == torch.float32 else 2
+        in0 = torch.randn(rows, N, device=dev).to(dt).requires_grad_(True)
+        in1 = torch.randn(rows, N, device=dev).to(dt).requires_grad_(True) if has_in1 else None
+        skip = torch.randn(rows, Ns, device=dev).to(dt).requires_grad_(True) if Ns else None
+        gamma = torch.ones(N, device=dev, requires_grad=True)
+        beta = torch.zeros(N, device=dev, requires_grad=True)
+        dout = torch.randn(rows, N, device=dev).to(dt)
+        out = [None]
+
+        def fwd():
+            out[0] = norm_act(in0, gamma, beta, in1=in1, skip=skip, act=act, drop_p=p, seed=11)
+
+        def bwd():
+            torch.autograd.grad(out[0], [t for t in (in0, in1, skip, gamma, beta) if t is not None], dout,
+                                retain_graph=True)
+
+        nin = rows * N * s * (2 if has_in1 else 1) + (rows * Ns * s if Ns else 0)
+        fb = nin + rows * N * s                                   # inputs + out
+        bb = rows * N * s * (3 if not has_in1 else 4) + (rows * Ns * s if Ns else 0)   # dout, in0(+in1), d_in0, d_skip
+        from vit_spectre_experiments_b200.functional import TIMER
+        for which, fn, nbytes in (("fwd", fwd, fb), ("bwd", bwd, bb)):
+            # time the C-ABI call only (CUDA events around it), not the autograd / allocator plumbing
+            ts = []
+            for it in range(args.iters + 3):
+                flush.zero_()
+                TIMER.reset(); TIMER.enabled = True
+                fn()
+                TIMER.enabled = False
+                (n, ms, _), = TIMER.summary().values()
+                if it >= 3:
+                    ts.append(ms)
+            ts.sort()
+            med, best = ts[len(ts) // 2], ts[0]
+            print(json.dumps({
+                "kernel": f"norm_act_{which}", "shape": name, "ms_median": round(med, 4), "ms_best": round(best, 4),
+                "algo_MB": round(nbytes / 1e6, 2), "GBps_median": round(nbytes / med / 1e6, 1),
+                "frac_of_measured_peak": round(nbytes / med / 1e6 / PEAK, 3),
             }), flush=True)
 
 

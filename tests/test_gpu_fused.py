@@ -13,7 +13,7 @@ def rel_err(a, b):
 
 
 def ref_norm_act(in0, gamma, beta, in1, skip, act, eps=1e-5):
-    z = in0.float() if in1 is None else in0.float() + in1
+    z = in0 if in1 is None else in0 + in1
     u = F.layer_norm(z, (z.shape[-1],), gamma, beta, eps)
     if act == "gelu":
         u = F.gelu(u)
@@ -24,59 +24,84 @@ def ref_norm_act(in0, gamma, beta, in1, skip, act, eps=1e-5):
 
 
 CASES = [
-    # rows-shape, N, Ns, in0 dtype, in1, act      which line of the reference layer
+    # rows-shape, N, Ns, dtype, in1, act      which line of the reference layer
     ((6, 197), 384, 384, torch.bfloat16, False, "none"),    # x1 = LN1(mix) + x            (spectre.py:66)
     ((6, 197), 1536, 384, torch.bfloat16, False, "gelu"),   # GELU(LN(h1)) + pool_up(x1)    (layers.py:95-101)
     ((6, 197), 384, 1536, torch.bfloat16, False, "gelu"),   # GELU(LN(h2)) + pool_down(a1)
-    ((6, 197), 384, None, torch.float32, True, "none"),     # x2 = LN2(x1 + ff)            (spectre.py:67)
+    ((6, 197), 384, None, torch.bfloat16, True, "none"),    # x2 = LN2(x1 + ff)            (spectre.py:67)
+    ((6, 197), 384, 384, torch.float32, False, "none"),     # the same four in float32
+    ((6, 197), 1536, 384, torch.float32, False, "gelu"),
+    ((6, 197), 384, 1536, torch.float32, False, "gelu"),
+    ((6, 197), 384, None, torch.float32, True, "none"),
     ((3, 65), 768, 512, torch.float32, False, "gelu"),      # C1 widths: general adaptive pool 512 -> 768
     ((3, 65), 512, 768, torch.float32, False, "gelu"),      #            and 768 -> 512
     ((5, 50), 48, 48, torch.float32, False, "none"),        # C2 width 48 (single partial warp)
     ((5, 50), 256, 48, torch.float32, False, "gelu"),       # 48 -> 256 (general)
+    ((5, 50), 48, 256, torch.float32, False, "gelu"),       # 256 -> 48 (general)
     ((2, 197), 3072, 768, torch.bfloat16, False, "gelu"),   # ViT-B widths
     ((2, 197), 768, 3072, torch.bfloat16, False, "gelu"),
+    ((1, 37), 4096, 512, torch.float32, False, "gelu"),     # widest row (one CTA per row), ratio 8
+    ((1, 37), 512, 4096, torch.bfloat16, False, "none"),
+    ((1, 1), 128, 256, torch.float32, True, "gelu"),        # single row, ratio 2 down, with in1
+    ((7, 11), 256, 128, torch.bfloat16, True, "none"),      # ratio 2 up, with in1
 ]
 
 
 @pytest.mark.parametrize("shape,N,Ns,dtype,has_in1,act", CASES)
 def test_norm_act_fwd_bwd(cuda_device, shape, N, Ns, dtype, has_in1, act):
+    """Tolerances (relative to the max magnitude of the reference tensor): float32 5e-6 forward / 2e-5 backward
+    (erf by the A&S 7.1.26 rational, |err| < 2e-7); bfloat16 1e-2 (output rounding only)."""
     from vit_spectre_experiments_b200.fused import norm_act
 
     g = torch.Generator().manual_seed(N * 7 + (Ns or 0))
     in0 = torch.randn(*shape, N, generator=g).to(dtype)
-    in1 = torch.randn(*shape, N, generator=g) if has_in1 else None
-    skip = torch.randn(*shape, Ns, generator=g) if Ns else None
+    in1 = torch.randn(*shape, N, generator=g).to(dtype) if has_in1 else None
+    skip = torch.randn(*shape, Ns, generator=g).to(dtype) if Ns else None
     gamma = 1 + 0.3 * torch.randn(N, generator=g)
     beta = 0.2 * torch.randn(N, generator=g)
-    dout = torch.randn(*shape, N, generator=g)
-    dout_b = torch.randn(*shape, N, generator=g).to(torch.bfloat16)
+    dout = torch.randn(*shape, N, generator=g).to(dtype)
 
     def leaf(t):
         return None if t is None else t.clone().requires_grad_(True)
 
-    # reference (fp32 torch on the same, bf16-rounded, inputs)
-    r = [leaf(in0.float()), leaf(gamma), leaf(beta), leaf(in1), leaf(skip)]
+    # reference (fp32 torch on the same, dtype-rounded, inputs)
+    r = [leaf(None if t is None else t.float()) for t in (in0, gamma, beta, in1, skip)]
     y_ref = ref_norm_act(r[0], r[1], r[2], r[3], r[4], act)
-    (y_ref * dout).sum().backward() if dtype == torch.float32 else (y_ref * (dout + dout_b.float())).sum().backward()
+    (y_ref * dout.float()).sum().backward()
 
-    d = [None if t is None else t.to(cuda_device) for t in (in0, gamma, beta, in1, skip)]
-    d = [leaf(t) for t in d]
-    want_twin = dtype == torch.bfloat16
-    y, yb = norm_act(d[0], d[1], d[2], in1=d[3], skip=d[4], act=act, want_bf16=want_twin)
-    assert y.dtype == torch.float32 and rel_err(y, y_ref) <= 2e-6
-    if want_twin:
-        assert yb.dtype == torch.bfloat16 and rel_err(yb, y_ref.to(torch.bfloat16)) <= 1e-2
-        torch.autograd.backward([y, yb], [dout.to(cuda_device), dout_b.to(cuda_device)])
-    else:
-        assert yb is None
-        y.backward(dout.to(cuda_device))
-    tol_in0 = 1e-5 if dtype == torch.float32 else 1e-2       # d_in0 is rounded to in0's dtype
-    assert d[0].grad.dtype == dtype and rel_err(d[0].grad, r[0].grad) <= tol_in0
-    assert rel_err(d[1].grad, r[1].grad) <= 2e-5 and rel_err(d[2].grad, r[2].grad) <= 2e-5
+    d = [leaf(None if t is None else t.to(cuda_device)) for t in (in0, gamma, beta, in1, skip)]
+    y = norm_act(d[0], d[1], d[2], in1=d[3], skip=d[4], act=act)
+    bf = dtype == torch.bfloat16
+    assert y.dtype == dtype and rel_err(y, y_ref) <= (1e-2 if bf else 5e-6)
+    y.backward(dout.to(cuda_device))
+    tol = 1e-2 if bf else 2e-5
+    assert d[0].grad.dtype == dtype and rel_err(d[0].grad, r[0].grad) <= tol
+    assert rel_err(d[1].grad, r[1].grad) <= 3e-5 and rel_err(d[2].grad, r[2].grad) <= 3e-5
     if has_in1:
-        assert rel_err(d[3].grad, r[3].grad) <= 1e-5
+        assert rel_err(d[3].grad, r[3].grad) <= tol
     if Ns:
-        assert rel_err(d[4].grad, r[4].grad) <= 1e-5
+        assert rel_err(d[4].grad, r[4].grad) <= tol
+
+
+def test_norm_act_large_rows_deterministic(cuda_device):
+    """Many rows (several row groups per CTA, partial last group): gamma/beta gradients are bit-identical
+    between runs (fixed-order partial sums, no atomics) and match torch."""
+    from vit_spectre_experiments_b200.fused import norm_act
+
+    torch.manual_seed(5)
+    x = torch.randn(20011, 384, device=cuda_device)
+    gamma = (1 + 0.1 * torch.randn(384, device=cuda_device)).requires_grad_(True)
+    beta = torch.zeros(384, device=cuda_device, requires_grad=True)
+    w = torch.randn_like(x)
+    grads = []
+    for _ in range(2):
+        gamma.grad = beta.grad = None
+        (norm_act(x, gamma, beta, act="gelu") * w).sum().backward()
+        grads.append((gamma.grad.clone(), beta.grad.clone()))
+    assert torch.equal(grads[0][0], grads[1][0]) and torch.equal(grads[0][1], grads[1][1])
+    g2, b2 = gamma.detach().clone().requires_grad_(True), beta.detach().clone().requires_grad_(True)
+    (F.gelu(F.layer_norm(x, (384,), g2, b2)) * w).sum().backward()
+    assert rel_err(grads[0][0], g2.grad) <= 3e-5 and rel_err(grads[0][1], b2.grad) <= 3e-5
 
 
 def test_norm_act_dropout_is_consistent(cuda_device):
@@ -85,13 +110,18 @@ def test_norm_act_dropout_is_consistent(cuda_device):
 
     x = torch.randn(64, 197, 384, device=cuda_device).requires_grad_(True)
     gamma, beta = torch.ones(384, device=cuda_device), torch.zeros(384, device=cuda_device)
-    y0, _ = norm_act(x, gamma, beta)
-    y, _ = norm_act(x, gamma, beta, drop_p=0.25, seed=1234)
+    y0 = norm_act(x, gamma, beta)
+    y = norm_act(x, gamma, beta, drop_p=0.25, seed=1234)
     kept = y != 0
     assert abs(kept.float().mean().item() - 0.75) < 5e-3
     assert torch.allclose(y[kept], y0[kept] / 0.75, rtol=1e-6, atol=1e-6)
-    y2, _ = norm_act(x, gamma, beta, drop_p=0.25, seed=1234)
+    y2 = norm_act(x, gamma, beta, drop_p=0.25, seed=1234)
     assert torch.equal(y, y2)
+    y3 = norm_act(x, gamma, beta, drop_p=0.25, seed=1235)
+    assert not torch.equal(y, y3)
+    # small p (the configs use 0.001): keep-rate still right
+    y4 = norm_act(x, gamma, beta, drop_p=0.001, seed=7)
+    assert abs((y4 == 0).float().mean().item() - 0.001) < 2e-4
     # gradient flows only through kept elements: d/dx of sum(y * w) with w = 1 on dropped positions is 0
     (y * (~kept).float()).sum().backward()
     assert x.grad.abs().max().item() == 0.0
@@ -116,7 +146,7 @@ def test_encoder_layer_fused_matches_torch(cuda_device, autocast):
     w = torch.randn_like(ya)
     (ya * w).sum().backward()
     (yb * w).sum().backward()
-    tol = 2e-2 if autocast else 2e-5
+    tol = 3e-2 if autocast else 2e-5   # autocast: bf16 residual stream vs torch's fp32 LayerNorm outputs
     assert rel_err(ya, yb) <= tol and rel_err(xa.grad, xb.grad) <= tol
     pa, pb = dict(a.named_parameters()), dict(b.named_parameters())
     for k in pa:

@@ -6,84 +6,190 @@
 //   x1 = LN1(mix(x)) + x                      spectre_vit/models/spectre/spectre.py:66       (in0 = mix, skip = x)
 //   a  = GELU(LN(Linear(x))) + avg_pool(x)    spectre_vit/models/spectre/layers.py:95-101    (in0 = Linear(x), skip = x)
 //   x2 = LN2(x1 + ff)                         spectre.py:67                                  (in0 = x1, in1 = ff)
-// and its backward (d_in0, d_in1, d_skip, dgamma, dbeta) in ONE pass over the rows each way, instead of
+// and its backward (d_in0 = d_in1, d_skip, dgamma, dbeta) in ONE pass over the rows each way, instead of
 // the 6-10 elementwise / reduction launches of the stock composition (LayerNorm backward's gamma/beta
 // reduction and the adaptive-pool kernels were 50 % of the ViT-S/16 step: profiles/r01_step_profile_c4.txt).
 //
-// Mapping: one CTA = one row at a time (grid-stride over rows); a thread owns VPT vectors of 8 consecutive
-// columns (16-byte bf16 / 2x16-byte fp32 accesses, fully coalesced), so the per-column gamma/beta gradient
-// accumulators live in registers across the whole row loop; row statistics are a warp shuffle + one small
-// shared-memory exchange.  All arithmetic is fp32 (autocast runs layer_norm / gelu in fp32).
+// Every activation tensor of a call has ONE element type T (float32, or bfloat16 for the bf16 training
+// stream); statistics, gamma/beta and all arithmetic are fp32.
+//
+// Mapping: a row is owned by TPR threads (a whole number of warps); a thread owns VPT vectors of 8
+// consecutive columns (16-byte bf16 / 2x16-byte fp32 accesses, coalesced).  A CTA of up to 256 threads
+// carries RPC = 256 / TPR rows at a time (narrow rows: one warp per row, no barrier at all) and strides
+// over the rows, so the per-column gamma/beta gradient accumulators stay in registers for the whole
+// kernel and are folded across the CTA's rows in shared memory before ONE partial per CTA is written.
+// Loads are decoupled from the math: the rows of a group are contiguous in every operand, so ONE thread
+// issues one bulk async copy (cp.async.bulk, the 1-D TMA path) per operand per group into a 2-4 stage
+// shared-memory ring, completion on an mbarrier -- tens of KB in flight per SM at any time without
+// holding registers for them.  Results go straight from registers to HBM with 16-byte stores.
+// The kernels are instruction-bound next to the GELU (erf) and the dropout mask, hence: erf by the
+// Abramowitz-Stegun 7.1.26 rational (|err| < 2e-7, one exp shared with the Gaussian of the derivative),
+// a 32-bit counter hash per element, pooling ratios resolved at compile time.
 #include <cstdarg>
+#include <utility>
 
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 namespace sb200 {
 namespace na {
 
-enum : int { kSkipNone = 0, kSkipIdentity = 1, kSkipUp = 2, kSkipDown = 3, kSkipGeneral = 4 };
+// skip variants; every kernel instantiation carries exactly one (lean inner loops, small code)
+enum : int { kSkipNone = 0, kSkipIdentity = 1, kSkipUp2 = 2, kSkipUp4 = 3, kSkipUp8 = 4, kSkipDown2 = 5, kSkipDown4 = 6,
+             kSkipDown8 = 7, kSkipGeneral = 8, kSkipModes = 9 };
+constexpr int up_k(int mode) { return mode == kSkipUp2 ? 2 : mode == kSkipUp4 ? 4 : mode == kSkipUp8 ? 8 : 0; }
+constexpr int down_k(int mode) { return mode == kSkipDown2 ? 2 : mode == kSkipDown4 ? 4 : mode == kSkipDown8 ? 8 : 0; }
 
 struct Args {
-  const void* in0; const float* in1; const float* gamma; const float* beta; const float* skip;
-  float* out; void* out_bf16; float* mean; float* rstd;
-  const float* dout; const void* dout_bf16;
-  void* d_in0; float* d_in1; float* d_skip; float* part;   // part: [grid][2][N] gamma/beta partials
-  long long rows; int N; int Ns; int act; int skip_mode; int k;   // k = N/Ns (up) or Ns/N (down)
-  float eps; float drop_p; unsigned long long seed;
+  const void* in0; const void* in1; const float* gamma; const float* beta; const void* skip;
+  void* out; float* mean; float* rstd;
+  const void* dout;
+  void* d_in0; void* d_skip; float* part;   // part: [grid][2][N] gamma/beta partials
+  long long rows; int N; int Ns; int act; int skip_mode;
+  int tpr; int rpc;                                                 // threads per row, rows per CTA
+  int stages; int stage_bytes;                                      // shared-memory ring of input row groups
+  float eps; float drop_p; unsigned seed_lo; unsigned seed_hi;
 };
 
-// ------------------------------------------------------------------ small helpers
+// ------------------------------------------------------------------ typed vector I/O
+__device__ __forceinline__ float bf_lo(unsigned u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf_hi(unsigned u) { return __uint_as_float(u & 0xffff0000u); }
+__device__ __forceinline__ unsigned bf_pack(float lo, float hi) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const unsigned*>(&h);
+}
+
+// 1-D bulk async copy global -> shared (16-byte aligned, size a multiple of 16), completion on an mbarrier
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(ptx::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(ptx::smem_u32(bar)) : "memory");
+}
+constexpr int kMaxStages = 4;
+
 __device__ __forceinline__ void ld8(const float* p, float (&v)[8]) {
   const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
   v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 }
 __device__ __forceinline__ void ld8(const __nv_bfloat16* p, float (&v)[8]) {
   const uint4 q = *reinterpret_cast<const uint4*>(p);
-  const unsigned u[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    v[2 * i] = __uint_as_float(u[i] << 16);
-    v[2 * i + 1] = __uint_as_float(u[i] & 0xffff0000u);
-  }
+  v[0] = bf_lo(q.x); v[1] = bf_hi(q.x); v[2] = bf_lo(q.y); v[3] = bf_hi(q.y);
+  v[4] = bf_lo(q.z); v[5] = bf_hi(q.z); v[6] = bf_lo(q.w); v[7] = bf_hi(q.w);
 }
 __device__ __forceinline__ void st8(float* p, const float (&v)[8]) {
   *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
   *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
 }
 __device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&v)[8]) {
-  unsigned u[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-    u[i] = *reinterpret_cast<const unsigned*>(&h);
-  }
-  *reinterpret_cast<uint4*>(p) = make_uint4(u[0], u[1], u[2], u[3]);
+  *reinterpret_cast<uint4*>(p) =
+      make_uint4(bf_pack(v[0], v[1]), bf_pack(v[2], v[3]), bf_pack(v[4], v[5]), bf_pack(v[6], v[7]));
 }
+// n in {1, 2, 4} consecutive elements (n * sizeof(T) aligned)
+template <int n>
+__device__ __forceinline__ void ldn(const float* p, float (&v)[n]) {
+  if constexpr (n == 4) { const float4 a = *reinterpret_cast<const float4*>(p); v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; }
+  else if constexpr (n == 2) { const float2 a = *reinterpret_cast<const float2*>(p); v[0] = a.x; v[1] = a.y; }
+  else v[0] = *p;
+}
+template <int n>
+__device__ __forceinline__ void ldn(const __nv_bfloat16* p, float (&v)[n]) {
+  if constexpr (n == 4) { const uint2 a = *reinterpret_cast<const uint2*>(p); v[0] = bf_lo(a.x); v[1] = bf_hi(a.x); v[2] = bf_lo(a.y); v[3] = bf_hi(a.y); }
+  else if constexpr (n == 2) { const unsigned a = *reinterpret_cast<const unsigned*>(p); v[0] = bf_lo(a); v[1] = bf_hi(a); }
+  else v[0] = __bfloat162float(*p);
+}
+template <int n>
+__device__ __forceinline__ void stn(float* p, const float (&v)[n]) {
+  if constexpr (n == 4) *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  else if constexpr (n == 2) *reinterpret_cast<float2*>(p) = make_float2(v[0], v[1]);
+  else *p = v[0];
+}
+template <int n>
+__device__ __forceinline__ void stn(__nv_bfloat16* p, const float (&v)[n]) {
+  if constexpr (n == 4) *reinterpret_cast<uint2*>(p) = make_uint2(bf_pack(v[0], v[1]), bf_pack(v[2], v[3]));
+  else if constexpr (n == 2) *reinterpret_cast<unsigned*>(p) = bf_pack(v[0], v[1]);
+  else *p = __float2bfloat16_rn(v[0]);
+}
+__device__ __forceinline__ float ld1(const float* p) { return *p; }   // also reads the shared-memory ring: no __ldg
+__device__ __forceinline__ float ld1(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ void st1(float* p, float v) { *p = v; }
+__device__ __forceinline__ void st1(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
 
-// exact (erf) GELU, as nn.GELU() in layers.py:89
-__device__ __forceinline__ float gelu(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// ------------------------------------------------------------------ GELU (erf form, nn.GELU() of layers.py:89)
+// erf(|u|) = 1 - (a1 t + ... + a5 t^5) exp(-u^2),  t = 1 / (1 + p |u|)      (Abramowitz & Stegun 7.1.26)
+// returns Phi(x) = 0.5 (1 + erf(x / sqrt 2)) and, through *gauss, exp(-x^2 / 2)
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float norm_cdf(float x, float* gauss) {
+  const float t = rcp_approx(fmaf(0.3275911f * 0.70710678118654752f, fabsf(x), 1.0f));
+  const float e = ex2_approx(x * x * -0.72134752044448170f);     // exp(-x^2 / 2)
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float half_tail = 0.5f * poly * t * e;        // 0.5 * erfc(|x| / sqrt 2)
+  *gauss = e;
+  return x >= 0.f ? 1.0f - half_tail : half_tail;
+}
+__device__ __forceinline__ float gelu(float x) {
+  float g;
+  return x * norm_cdf(x, &g);
+}
 __device__ __forceinline__ float gelu_grad(float x) {
-  return 0.5f * (1.0f + erff(x * 0.70710678118654752f)) + x * 0.39894228040143268f * __expf(-0.5f * x * x);
+  float g;
+  const float cdf = norm_cdf(x, &g);
+  return fmaf(x * 0.39894228040143268f, g, cdf);
 }
 
-// counter-based dropout: keep-mask of element idx under (seed); one 64-bit mix per element
-__device__ __forceinline__ bool keep(unsigned long long seed, unsigned long long idx, unsigned thresh) {
-  unsigned long long z = seed + idx * 0x9E3779B97F4A7C15ull;
+// counter-based dropout.  A vector of 8 columns shares one well-mixed 32-bit word (lowbias32 of the vector
+// index under the row seed); element e takes one more odd multiply + xorshift of it, and is kept iff the
+// result >= drop_p * 2^32.  Forward, backward and the general-pool transpose all go through keep().
+__device__ __forceinline__ unsigned vec_hash(unsigned seed, unsigned vec) {
+  unsigned x = vec ^ seed;
+  x ^= x >> 16; x *= 0x7feb352du;
+  x ^= x >> 15; x *= 0x846ca68bu;
+  x ^= x >> 16;
+  return x;
+}
+__device__ __forceinline__ bool keep_e(unsigned vh, int e, unsigned thresh) {
+  constexpr unsigned kMul[8] = {0x9E3779B1u, 0x85EBCA77u, 0xC2B2AE3Du, 0x27D4EB2Fu, 0x165667B1u, 0xD3A2646Du, 0xFD7046C5u, 0xB55A4F09u};
+  unsigned x = vh * kMul[e];
+  x ^= x >> 15;
+  return x >= thresh;
+}
+__device__ __forceinline__ bool keep(unsigned seed, unsigned idx, unsigned thresh) {
+  const unsigned vh = vec_hash(seed, idx >> 3);
+  unsigned x = vh;
+  switch (idx & 7) {
+    case 0: return keep_e(x, 0, thresh); case 1: return keep_e(x, 1, thresh); case 2: return keep_e(x, 2, thresh);
+    case 3: return keep_e(x, 3, thresh); case 4: return keep_e(x, 4, thresh); case 5: return keep_e(x, 5, thresh);
+    case 6: return keep_e(x, 6, thresh); default: return keep_e(x, 7, thresh);
+  }
+}
+// seed of a row: folds the high bits of the 64-bit seed and the row index so idx can stay 32-bit (column)
+__device__ __forceinline__ unsigned row_seed(const Args& a, long long row) {
+  unsigned long long z = (static_cast<unsigned long long>(a.seed_hi) << 32 | a.seed_lo) + static_cast<unsigned long long>(row) * 0x9E3779B97F4A7C15ull;
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-  z ^= z >> 31;
-  return static_cast<unsigned>(z >> 32) >= thresh;
+  z ^= z >> 27;
+  return static_cast<unsigned>(z >> 16);
 }
 
-// sum over the CTA of up to two values; `slot` alternates so consecutive calls need one barrier each
+// sum over the threads of one row of NV values.  One warp per row: shuffles only.  Several warps per row:
+// one CTA-wide barrier (every row group of the CTA executes the same trip count); `slot` alternates so
+// consecutive calls need one barrier each.
 template <int NV>
-__device__ __forceinline__ void block_sum(float (&v)[NV], float (*red)[NV][8], int slot) {
+__device__ __forceinline__ void row_sum(float (&v)[NV], float (*red)[NV][8], int slot, int wpr, int rg) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
     for (int i = 0; i < NV; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
-  const int nw = blockDim.x >> 5;
-  if (nw > 1) {
+  if (wpr > 1) {
     const int w = threadIdx.x >> 5;
     if ((threadIdx.x & 31) == 0)
 #pragma unroll
@@ -92,42 +198,125 @@ __device__ __forceinline__ void block_sum(float (&v)[NV], float (*red)[NV][8], i
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       float s = 0.f;
-      for (int k = 0; k < nw; ++k) s += red[slot][i][k];
+      for (int k = 0; k < wpr; ++k) s += red[slot][i][rg * wpr + k];
       v[i] = s;
     }
   }
 }
 
-// pooled skip value for output column j (adaptive average pool Ns -> N, torch semantics)
-__device__ __forceinline__ float pool_general(const float* srow, int j, int N, int Ns) {
+// adaptive average pool Ns -> N (torch semantics), general widths: value for output column j
+template <class T>
+__device__ __forceinline__ float pool_general(const T* srow, int j, int N, int Ns) {
   const int s = static_cast<int>((static_cast<long long>(j) * Ns) / N);
   const int e = static_cast<int>((static_cast<long long>(j + 1) * Ns + N - 1) / N);
   float acc = 0.f;
-  for (int i = s; i < e; ++i) acc += __ldg(srow + i);
+  for (int i = s; i < e; ++i) acc += ld1(srow + i);
   return acc / static_cast<float>(e - s);
 }
 
+// o[0..8) += pool(skip)[j0 .. j0+8) for integer ratios resolved at compile time
+template <class T, int K>
+__device__ __forceinline__ void skip_up_add(const T* srow, int j0, float (&o)[8]) {
+  float s[8 / K];
+  ldn<8 / K>(srow + j0 / K, s);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) o[e] += s[e / K];
+}
+template <class T, int K>
+__device__ __forceinline__ void skip_down_add(const T* srow, int j0, float (&o)[8]) {
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll
+  for (int v = 0; v < K; ++v) {
+    float s[8];
+    ld8(srow + static_cast<long long>(j0) * K + v * 8, s);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[(v * 8 + i) / K] += s[i];
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) o[e] = fmaf(acc[e], 1.0f / K, o[e]);
+}
+// transposes: d_skip from the (masked) upstream gradient d[0..8) of columns j0 .. j0+8
+template <class T, int K>
+__device__ __forceinline__ void skip_up_bwd(T* drow, int j0, const float (&d)[8]) {
+  float s[8 / K];
+#pragma unroll
+  for (int i = 0; i < 8 / K; ++i) {
+    float acc = 0.f;
+#pragma unroll
+    for (int r = 0; r < K; ++r) acc += d[i * K + r];
+    s[i] = acc;
+  }
+  stn<8 / K>(drow + j0 / K, s);
+}
+template <class T, int K>
+__device__ __forceinline__ void skip_down_bwd(T* drow, int j0, const float (&d)[8]) {
+#pragma unroll
+  for (int v = 0; v < K; ++v) {
+    float s[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = d[(v * 8 + i) / K] * (1.0f / K);
+    st8(drow + static_cast<long long>(j0) * K + v * 8, s);
+  }
+}
+
 // ------------------------------------------------------------------ forward
-template <class T0, int VPT>
-__global__ void __launch_bounds__(256) norm_act_fwd_kernel(const Args a) {
-  __shared__ float red[3][1][8];
-  const int t = threadIdx.x, nvec = a.N >> 3;
+template <class T, int VPT, int MODE>
+__global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
+  extern __shared__ __align__(128) uint8_t ring[];
+  __shared__ uint64_t full[kMaxStages];
+  __shared__ float red[2][1][8];
+  const int tpr = a.tpr, wpr = tpr >> 5;
+  const int rg = threadIdx.x / tpr, t = threadIdx.x - rg * tpr;
+  const int nvec = a.N >> 3, S = a.stages;
   const float inv_n = 1.0f / static_cast<float>(a.N);
   const bool drop = a.drop_p > 0.f;
   const unsigned thresh = drop ? static_cast<unsigned>(fminf(a.drop_p, 0.999999f) * 4294967296.0f) : 0u;
   const float keep_scale = drop ? 1.0f / (1.0f - a.drop_p) : 1.0f;
-  for (long long row = blockIdx.x; row < a.rows; row += gridDim.x) {
-    const T0* r0 = static_cast<const T0*>(a.in0) + row * a.N;
+  const long long groups = (a.rows + a.rpc - 1) / a.rpc;
+  const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  const int off_in1 = a.rpc * a.N * static_cast<int>(sizeof(T));
+  const int off_skip = off_in1 * (a.in1 ? 2 : 1);
+
+  auto issue = [&](int it, int stg) {   // one thread: the group's rows are contiguous in every operand
+    const long long row0 = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc;
+    const long long left = a.rows - row0;
+    const uint32_t nr = static_cast<uint32_t>(left < a.rpc ? left : a.rpc);
+    uint8_t* st = ring + stg * a.stage_bytes;
+    uint64_t* bar = &full[stg];
+    const uint32_t bmain = nr * a.N * sizeof(T), bskip = MODE != kSkipNone ? nr * a.Ns * static_cast<uint32_t>(sizeof(T)) : 0u;
+    ptx::mbar_arrive_expect_tx(bar, bmain * (a.in1 ? 2u : 1u) + bskip);
+    bulk_load(st, static_cast<const T*>(a.in0) + row0 * a.N, bmain, bar);
+    if (a.in1) bulk_load(st + off_in1, static_cast<const T*>(a.in1) + row0 * a.N, bmain, bar);
+    if (MODE != kSkipNone) bulk_load(st + off_skip, static_cast<const T*>(a.skip) + row0 * a.Ns, bskip, bar);
+  };
+  if (threadIdx.x == 0) {
+    for (int k = 0; k < S; ++k) ptx::mbar_init(&full[k], 1);
+    ptx::mbar_fence_init();
+    for (int it = 0; it < S - 1 && it < n_it; ++it) issue(it, it);
+  }
+  __syncthreads();
+
+  int stg = 0;
+  uint32_t phase = 0;
+  for (int it = 0; it < n_it; ++it) {
+    if (threadIdx.x == 0 && it + S - 1 < n_it) issue(it + S - 1, stg == 0 ? S - 1 : stg - 1);   // the stage freed by it-1
+    ptx::mbar_wait(&full[stg], phase);
+    const long long row = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc + rg;
+    const bool live = row < a.rows;
+    const uint8_t* st = ring + stg * a.stage_bytes;
+    const T* r0 = reinterpret_cast<const T*>(st) + rg * a.N;
     float z[VPT][8];
     float s[1] = {0.f};
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
-      const int v = t + i * blockDim.x;
-      if (v < nvec) {
+      const int v = t + i * tpr;
+      if (live && v < nvec) {
         ld8(r0 + v * 8, z[i]);
         if (a.in1) {
           float w[8];
-          ld8(a.in1 + row * a.N + v * 8, w);
+          ld8(reinterpret_cast<const T*>(st + off_in1) + rg * a.N + v * 8, w);
 #pragma unroll
           for (int e = 0; e < 8; ++e) z[i][e] += w[e];
         }
@@ -138,199 +327,219 @@ __global__ void __launch_bounds__(256) norm_act_fwd_kernel(const Args a) {
         for (int e = 0; e < 8; ++e) z[i][e] = 0.f;
       }
     }
-    block_sum<1>(s, red, 0);
+    row_sum<1>(s, red, 0, wpr, rg);
     const float mean = s[0] * inv_n;
     float q[1] = {0.f};
 #pragma unroll
     for (int i = 0; i < VPT; ++i)
-      if (t + i * blockDim.x < nvec)
+      if (t + i * tpr < nvec)
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           const float d = z[i][e] - mean;
-          q[0] += d * d;
+          q[0] = fmaf(d, d, q[0]);
         }
-    block_sum<1>(q, red, 1);
-    const float rstd = rsqrtf(q[0] * inv_n + a.eps);
-    if (t == 0) {
-      a.mean[row] = mean;
-      a.rstd[row] = rstd;
-    }
-    const float* srow = a.skip ? a.skip + row * a.Ns : nullptr;
-#pragma unroll
-    for (int i = 0; i < VPT; ++i) {
-      const int v = t + i * blockDim.x;
-      if (v >= nvec) continue;
-      const int j0 = v * 8;
-      float g[8], b[8], o[8];
-      ld8(a.gamma + j0, g);
-      ld8(a.beta + j0, b);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float u = (z[i][e] - mean) * rstd * g[e] + b[e];
-        o[e] = a.act ? gelu(u) : u;
+    row_sum<1>(q, red, 1, wpr, rg);
+    if (live) {
+      const float rstd = rsqrtf(q[0] * inv_n + a.eps);
+      if (t == 0) {
+        a.mean[row] = mean;
+        a.rstd[row] = rstd;
       }
-      if (a.skip_mode == kSkipIdentity) {
-        float sk[8];
-        ld8(srow + j0, sk);
+      const float shift = -mean * rstd;
+      const T* srow = reinterpret_cast<const T*>(st + off_skip) + rg * a.Ns;
+      const unsigned rseed = drop ? row_seed(a, row) : 0u;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] += sk[e];
-      } else if (a.skip_mode == kSkipUp) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] += __ldg(srow + (j0 + e) / a.k);
-      } else if (a.skip_mode == kSkipDown) {
-        const float inv_k = 1.0f / static_cast<float>(a.k);
-        const float* sp = srow + static_cast<long long>(j0) * a.k;
+      for (int i = 0; i < VPT; ++i) {
+        const int v = t + i * tpr;
+        if (v >= nvec) continue;
+        const int j0 = v * 8;
+        float g[8], b[8], o[8];
+        ld8(a.gamma + j0, g);
+        ld8(a.beta + j0, b);
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          float acc = 0.f;
-          if ((a.k & 3) == 0) {
-            for (int r = 0; r < a.k; r += 4) {
-              const float4 f = *reinterpret_cast<const float4*>(sp + e * a.k + r);
-              acc += (f.x + f.y) + (f.z + f.w);
-            }
-          } else {
-            for (int r = 0; r < a.k; ++r) acc += sp[e * a.k + r];
-          }
-          o[e] += acc * inv_k;
+          const float u = fmaf(fmaf(z[i][e], rstd, shift), g[e], b[e]);
+          o[e] = a.act ? gelu(u) : u;
         }
-      } else if (a.skip_mode == kSkipGeneral) {
+        if constexpr (MODE == kSkipIdentity) {
+          float sk[8];
+          ld8(srow + j0, sk);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] += pool_general(srow, j0 + e, a.N, a.Ns);
-      }
-      if (drop) {
-        const unsigned long long base = static_cast<unsigned long long>(row) * a.N + j0;
+          for (int e = 0; e < 8; ++e) o[e] += sk[e];
+        } else if constexpr (up_k(MODE) > 0) {
+          skip_up_add<T, up_k(MODE)>(srow, j0, o);
+        } else if constexpr (down_k(MODE) > 0) {
+          skip_down_add<T, down_k(MODE)>(srow, j0, o);
+        } else if constexpr (MODE == kSkipGeneral) {
+#pragma unroll 1
+          for (int e = 0; e < 8; ++e) o[e] += pool_general(srow, j0 + e, a.N, a.Ns);
+        }
+        if (drop) {
+          const unsigned vh = vec_hash(rseed, static_cast<unsigned>(v));
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] = keep(a.seed, base + e, thresh) ? o[e] * keep_scale : 0.f;
+          for (int e = 0; e < 8; ++e) o[e] = keep_e(vh, e, thresh) ? o[e] * keep_scale : 0.f;
+        }
+        st8(static_cast<T*>(a.out) + row * a.N + j0, o);
       }
-      st8(a.out + row * a.N + j0, o);
-      if (a.out_bf16) st8(static_cast<__nv_bfloat16*>(a.out_bf16) + row * a.N + j0, o);
     }
+    __syncthreads();   // every thread is done with this stage: the producer may refill it
+    if (++stg == S) { stg = 0; phase ^= 1u; }
   }
 }
 
 // ------------------------------------------------------------------ backward
-// d = (dout + dout_bf16) * dropout_mask ; d_skip = pool^T(d) ; g = d * act'(u) ; LayerNorm backward of g.
-template <class T0, int VPT>
-__global__ void __launch_bounds__(256) norm_act_bwd_kernel(const Args a) {
+// d = dout * dropout_mask ; d_skip = pool^T(d) ; g = d * act'(u) ; LayerNorm backward of g.
+template <class T, int VPT, int MODE>
+__global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
+  extern __shared__ __align__(128) uint8_t ring[];
+  __shared__ uint64_t full[kMaxStages];
   __shared__ float red[2][2][8];
-  const int t = threadIdx.x, nvec = a.N >> 3;
+  const int tpr = a.tpr, wpr = tpr >> 5;
+  const int rg = threadIdx.x / tpr, t = threadIdx.x - rg * tpr;
+  const int nvec = a.N >> 3, S = a.stages;
+  // per-row-group gamma/beta gradient accumulators [rpc][2][N] (a thread only ever touches its own columns
+  // of its own row group: no conflicts, and 32 registers less than keeping them in the register file)
+  float* accs = reinterpret_cast<float*>(ring + S * a.stage_bytes);
+  float* sgam = accs + a.rpc * 2 * a.N;                               // [N] gamma, [N] beta
+  float* myacc = accs + rg * 2 * a.N;
   const float inv_n = 1.0f / static_cast<float>(a.N);
   const bool drop = a.drop_p > 0.f;
   const unsigned thresh = drop ? static_cast<unsigned>(fminf(a.drop_p, 0.999999f) * 4294967296.0f) : 0u;
   const float keep_scale = drop ? 1.0f / (1.0f - a.drop_p) : 1.0f;
-  float dg[VPT][8], db[VPT][8], gam[VPT][8], bet[VPT][8];
-#pragma unroll
-  for (int i = 0; i < VPT; ++i) {
-    const int v = t + i * blockDim.x;
-#pragma unroll
-    for (int e = 0; e < 8; ++e) dg[i][e] = db[i][e] = gam[i][e] = bet[i][e] = 0.f;
-    if (v < nvec) {
-      ld8(a.gamma + v * 8, gam[i]);
-      if (a.act) ld8(a.beta + v * 8, bet[i]);
-    }
+  const long long groups = (a.rows + a.rpc - 1) / a.rpc;
+  const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  const int off_in0 = a.rpc * a.N * static_cast<int>(sizeof(T)), off_in1 = 2 * off_in0;
+
+  auto issue = [&](int it, int stg) {   // dout, in0 (, in1) of one row group: contiguous, one bulk copy each
+    const long long row0 = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc;
+    const long long left = a.rows - row0;
+    const uint32_t nr = static_cast<uint32_t>(left < a.rpc ? left : a.rpc);
+    uint8_t* st = ring + stg * a.stage_bytes;
+    uint64_t* bar = &full[stg];
+    const uint32_t bmain = nr * a.N * sizeof(T);
+    ptx::mbar_arrive_expect_tx(bar, bmain * (a.in1 ? 3u : 2u));
+    bulk_load(st, static_cast<const T*>(a.dout) + row0 * a.N, bmain, bar);
+    bulk_load(st + off_in0, static_cast<const T*>(a.in0) + row0 * a.N, bmain, bar);
+    if (a.in1) bulk_load(st + off_in1, static_cast<const T*>(a.in1) + row0 * a.N, bmain, bar);
+  };
+  if (threadIdx.x == 0) {
+    for (int k = 0; k < S; ++k) ptx::mbar_init(&full[k], 1);
+    ptx::mbar_fence_init();
+    for (int it = 0; it < S - 1 && it < n_it; ++it) issue(it, it);
   }
-  int parity = 0;
-  for (long long row = blockIdx.x; row < a.rows; row += gridDim.x, parity ^= 1) {
-    const T0* r0 = static_cast<const T0*>(a.in0) + row * a.N;
-    const float mean = a.mean[row], rstd = a.rstd[row];
+  for (int i = threadIdx.x; i < a.N; i += blockDim.x) {
+    sgam[i] = a.gamma[i];
+    sgam[a.N + i] = a.beta[i];
+  }
+  for (int i = threadIdx.x; i < a.rpc * 2 * a.N; i += blockDim.x) accs[i] = 0.f;
+  __syncthreads();
+
+  // row statistics of the first row (prefetched one iteration ahead afterwards)
+  float mean_n = 0.f, rstd_n = 0.f;
+  {
+    const long long row = static_cast<long long>(blockIdx.x) * a.rpc + rg;
+    if (n_it > 0 && row < a.rows) { mean_n = a.mean[row]; rstd_n = a.rstd[row]; }
+  }
+  int stg = 0;
+  uint32_t phase = 0;
+  for (int it = 0; it < n_it; ++it) {
+    if (threadIdx.x == 0 && it + S - 1 < n_it) issue(it + S - 1, stg == 0 ? S - 1 : stg - 1);
+    const long long row = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc + rg;
+    const bool live = row < a.rows;
+    const float mean = mean_n, rstd = rstd_n;
+    {
+      const long long rown = row + static_cast<long long>(gridDim.x) * a.rpc;
+      if (it + 1 < n_it && rown < a.rows) { mean_n = a.mean[rown]; rstd_n = a.rstd[rown]; }
+    }
+    ptx::mbar_wait(&full[stg], phase);
+    const uint8_t* st = ring + stg * a.stage_bytes;
+    const float shift = -mean * rstd;
+    const unsigned rseed = drop ? row_seed(a, row) : 0u;
     float xh[VPT][8], gy[VPT][8];
     float s[2] = {0.f, 0.f};
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
-      const int v = t + i * blockDim.x;
-      if (v >= nvec) {
+      const int v = t + i * tpr;
+      if (!live || v >= nvec) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) xh[i][e] = gy[i][e] = 0.f;
         continue;
       }
       const int j0 = v * 8;
-      float d[8];
-      ld8(a.dout + row * a.N + j0, d);
-      if (a.dout_bf16) {
-        float w[8];
-        ld8(static_cast<const __nv_bfloat16*>(a.dout_bf16) + row * a.N + j0, w);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) d[e] += w[e];
-      }
-      if (drop) {
-        const unsigned long long base = static_cast<unsigned long long>(row) * a.N + j0;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) d[e] = keep(a.seed, base + e, thresh) ? d[e] * keep_scale : 0.f;
-      }
-      // ---- skip path: transpose of the pooling
-      if (a.skip_mode == kSkipIdentity) {
-        st8(a.d_skip + row * a.Ns + j0, d);
-      } else if (a.skip_mode == kSkipUp) {         // N = k * Ns, k in {2,4,8}: 8/k skip columns per vector
-        float* dp = a.d_skip + row * a.Ns + j0 / a.k;
-        if (a.k == 2) {
-          *reinterpret_cast<float4*>(dp) = make_float4(d[0] + d[1], d[2] + d[3], d[4] + d[5], d[6] + d[7]);
-        } else if (a.k == 4) {
-          *reinterpret_cast<float2*>(dp) = make_float2((d[0] + d[1]) + (d[2] + d[3]), (d[4] + d[5]) + (d[6] + d[7]));
-        } else {
-          *dp = ((d[0] + d[1]) + (d[2] + d[3])) + ((d[4] + d[5]) + (d[6] + d[7]));
-        }
-      } else if (a.skip_mode == kSkipDown) {       // Ns = k * N: every skip column of the window gets d / k
-        const float inv_k = 1.0f / static_cast<float>(a.k);
-        float* dp = a.d_skip + row * a.Ns + static_cast<long long>(j0) * a.k;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float val = d[e] * inv_k;
-          if ((a.k & 3) == 0) {
-            for (int r = 0; r < a.k; r += 4) *reinterpret_cast<float4*>(dp + e * a.k + r) = make_float4(val, val, val, val);
-          } else {
-            for (int r = 0; r < a.k; ++r) dp[e * a.k + r] = val;
-          }
-        }
-      }
-      // ---- main path
-      float z[8];
-      ld8(r0 + j0, z);
+      float d[8], z[8];
+      ld8(reinterpret_cast<const T*>(st) + rg * a.N + j0, d);
+      ld8(reinterpret_cast<const T*>(st + off_in0) + rg * a.N + j0, z);
       if (a.in1) {
         float w[8];
-        ld8(a.in1 + row * a.N + j0, w);
+        ld8(reinterpret_cast<const T*>(st + off_in1) + rg * a.N + j0, w);
 #pragma unroll
         for (int e = 0; e < 8; ++e) z[e] += w[e];
       }
+      if (drop) {
+        const unsigned vh = vec_hash(rseed, static_cast<unsigned>(v));
+#pragma unroll
+        for (int e = 0; e < 8; ++e) d[e] = keep_e(vh, e, thresh) ? d[e] * keep_scale : 0.f;
+      }
+      // ---- skip path: transpose of the pooling
+      if constexpr (MODE == kSkipIdentity) {
+        st8(static_cast<T*>(a.d_skip) + row * a.Ns + j0, d);
+      } else if constexpr (up_k(MODE) > 0) {
+        skip_up_bwd<T, up_k(MODE)>(static_cast<T*>(a.d_skip) + row * a.Ns, j0, d);
+      } else if constexpr (down_k(MODE) > 0) {
+        skip_down_bwd<T, down_k(MODE)>(static_cast<T*>(a.d_skip) + row * a.Ns, j0, d);
+      }   // general widths: pool_bwd_general_kernel
+      // ---- main path
+      float gam[8], bet[8], dg[8], db[8];
+      ld8(sgam + j0, gam);
+      if (a.act) ld8(sgam + a.N + j0, bet);
+      ld8(myacc + j0, dg);
+      ld8(myacc + a.N + j0, db);
+      float s0 = 0.f, s1 = 0.f;
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
-        const float x = (z[e] - mean) * rstd;
+        const float x = fmaf(z[e], rstd, shift);
         float g = d[e];
-        if (a.act) g *= gelu_grad(x * gam[i][e] + bet[i][e]);
-        db[i][e] += g;
-        dg[i][e] += g * x;
-        const float y = g * gam[i][e];
+        if (a.act) g *= gelu_grad(fmaf(x, gam[e], bet[e]));
+        db[e] += g;
+        dg[e] = fmaf(g, x, dg[e]);
+        const float y = g * gam[e];
         xh[i][e] = x;
         gy[i][e] = y;
-        s[0] += y;
-        s[1] += y * x;
+        if (e & 1) { s1 = fmaf(y, x, s1); s[0] += y; } else { s[1] = fmaf(y, x, s[1]); s0 += y; }
+      }
+      s[0] += s0;
+      s[1] += s1;
+      st8(myacc + j0, dg);
+      st8(myacc + a.N + j0, db);
+    }
+    row_sum<2>(s, red, it & 1, wpr, rg);
+    if (live) {
+      const float m1 = s[0] * inv_n, m2 = s[1] * inv_n;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = t + i * tpr;
+        if (v >= nvec) continue;
+        float dz[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dz[e] = rstd * (gy[i][e] - m1 - xh[i][e] * m2);
+        st8(static_cast<T*>(a.d_in0) + row * a.N + v * 8, dz);
       }
     }
-    block_sum<2>(s, red, parity);
-    const float m1 = s[0] * inv_n, m2 = s[1] * inv_n;
-#pragma unroll
-    for (int i = 0; i < VPT; ++i) {
-      const int v = t + i * blockDim.x;
-      if (v >= nvec) continue;
-      float dz[8];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) dz[e] = rstd * (gy[i][e] - m1 - xh[i][e] * m2);
-      if (a.d_in0) st8(static_cast<T0*>(a.d_in0) + row * a.N + v * 8, dz);
-      if (a.d_in1) st8(a.d_in1 + row * a.N + v * 8, dz);
-    }
+    __syncthreads();   // stage consumed
+    if (++stg == S) { stg = 0; phase ^= 1u; }
   }
-  // per-CTA partial gamma / beta gradients
+  // fold the row groups of the CTA in a fixed order: one partial [2][N] per CTA  (the loop's last barrier
+  // already ordered every accumulator update)
   float* pg = a.part + static_cast<size_t>(blockIdx.x) * 2 * a.N;
-#pragma unroll
-  for (int i = 0; i < VPT; ++i) {
-    const int v = t + i * blockDim.x;
-    if (v < nvec) {
-      st8(pg + v * 8, dg[i]);
-      st8(pg + a.N + v * 8, db[i]);
-    }
+  for (int c = threadIdx.x; c < 2 * a.N; c += blockDim.x) {
+    float v = accs[c];
+    for (int r = 1; r < a.rpc; ++r) v += accs[r * 2 * a.N + c];
+    pg[c] = v;
   }
 }
 
 // general adaptive-pool transpose (only for widths that are not integer multiples): one thread per skip column
+template <class T>
 __global__ void pool_bwd_general_kernel(const Args a) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= a.rows * a.Ns) return;
@@ -341,47 +550,86 @@ __global__ void pool_bwd_general_kernel(const Args a) {
   const bool drop = a.drop_p > 0.f;
   const unsigned thresh = drop ? static_cast<unsigned>(fminf(a.drop_p, 0.999999f) * 4294967296.0f) : 0u;
   const float keep_scale = drop ? 1.0f / (1.0f - a.drop_p) : 1.0f;
+  const unsigned rseed = drop ? row_seed(a, row) : 0u;
   float acc = 0.f;
   for (int j = jlo; j < jhi; ++j) {
     const int s = static_cast<int>((static_cast<long long>(j) * a.Ns) / a.N);
     const int e = static_cast<int>((static_cast<long long>(j + 1) * a.Ns + a.N - 1) / a.N);
     if (c < s || c >= e) continue;
-    float d = a.dout[row * a.N + j];
-    if (a.dout_bf16) d += __bfloat162float(static_cast<const __nv_bfloat16*>(a.dout_bf16)[row * a.N + j]);
-    if (drop) d = keep(a.seed, static_cast<unsigned long long>(row) * a.N + j, thresh) ? d * keep_scale : 0.f;
+    float d = ld1(static_cast<const T*>(a.dout) + row * a.N + j);
+    if (drop) d = keep(rseed, static_cast<unsigned>(j), thresh) ? d * keep_scale : 0.f;
     acc += d / static_cast<float>(e - s);
   }
-  a.d_skip[i] = acc;
+  st1(static_cast<T*>(a.d_skip) + i, acc);
 }
 
-// dgamma[c] = sum_s part[s][0][c], dbeta[c] = sum_s part[s][1][c]  (fixed order: deterministic)
-__global__ void reduce_gamma_beta_kernel(const float* __restrict__ part, float* __restrict__ dgamma,
-                                         float* __restrict__ dbeta, int N, int slabs) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 2 * N) return;
-  float s = 0.f;
-  for (int k = 0; k < slabs; ++k) s += part[static_cast<size_t>(k) * 2 * N + i];
-  if (i < N) dgamma[i] = s;
-  else dbeta[i - N] = s;
+// dgamma[c] = sum_s part[s][0][c], dbeta[c] = sum_s part[s][1][c].  CTA = 32 columns x 8 slab lanes; the
+// eight lane sums are combined in a fixed order (deterministic).
+__global__ void __launch_bounds__(256) reduce_gamma_beta_kernel(const float* __restrict__ part, float* __restrict__ dgamma,
+                                                                float* __restrict__ dbeta, int N, int slabs) {
+  __shared__ float sm[8][33];
+  const int col = blockIdx.x * 32 + (threadIdx.x & 31), ln = threadIdx.x >> 5;
+  float s0 = 0.f, s1 = 0.f;
+  if (col < 2 * N) {
+    // 8 independent loads in flight per thread; partial sums are combined in a fixed order
+    float acc[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) acc[u] = 0.f;
+    int k = ln;
+    for (; k + 56 < slabs; k += 64) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc[u] += part[static_cast<size_t>(k + 8 * u) * 2 * N + col];
+    }
+    for (; k < slabs; k += 8) acc[0] += part[static_cast<size_t>(k) * 2 * N + col];
+    s0 = ((acc[0] + acc[1]) + (acc[2] + acc[3]));
+    s1 = ((acc[4] + acc[5]) + (acc[6] + acc[7]));
+  }
+  sm[ln][threadIdx.x & 31] = s0 + s1;
+  __syncthreads();
+  if (ln == 0 && col < 2 * N) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += sm[k][threadIdx.x];
+    if (col < N) dgamma[col] = s;
+    else dbeta[col - N] = s;
+  }
 }
 
 // ------------------------------------------------------------------ host side
-static int pick_skip(const spectre_norm_act_t& d, int* mode, int* k) {
-  *k = 1;
-  if (!d.skip) { *mode = kSkipNone; return 0; }
-  if (d.Ns == d.N) { *mode = kSkipIdentity; return 0; }
-  if (d.N % d.Ns == 0 && (d.N / d.Ns == 2 || d.N / d.Ns == 4 || d.N / d.Ns == 8)) { *mode = kSkipUp; *k = d.N / d.Ns; return 0; }
-  if (d.Ns % d.N == 0) { *mode = kSkipDown; *k = d.Ns / d.N; return 0; }
-  *mode = kSkipGeneral;
-  return 0;
+static int pick_skip(int N, int Ns, bool has_skip) {
+  if (!has_skip) return kSkipNone;
+  if (Ns == N) return kSkipIdentity;
+  const int up = N % Ns == 0 ? N / Ns : 0, down = Ns % N == 0 ? Ns / N : 0;
+  if (up == 2) return kSkipUp2;
+  if (up == 4) return kSkipUp4;
+  if (up == 8) return kSkipUp8;
+  if (down == 2) return kSkipDown2;
+  if (down == 4) return kSkipDown4;
+  if (down == 8) return kSkipDown8;
+  return kSkipGeneral;
 }
 
-static void launch_shape(int N, int* vpt, int* block) {
+// threads per row (whole warps), rows per CTA, vectors per thread, shared-memory ring
+struct Shape {
+  int vpt, tpr, rpc, stages, stage_bytes;
+  size_t smem;   // dynamic shared memory of the launch
+};
+static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, bool bwd) {
+  Shape sh{};
   const int nvec = N / 8;
-  if (nvec <= 32) { *vpt = 1; *block = 32; return; }
-  *vpt = 2;
-  int b = ((nvec + 1) / 2 + 31) / 32 * 32;
-  *block = b;
+  if (nvec <= 32) { sh.vpt = 1; sh.tpr = 32; }
+  else { sh.vpt = 2; sh.tpr = ((nvec + 1) / 2 + 31) / 32 * 32; }
+  // bytes of one row in the ring: forward in0 (+ in1) + skip; backward dout + in0 (+ in1)
+  const int row_bytes = bwd ? N * elem * (has_in1 ? 3 : 2) : N * elem * (has_in1 ? 2 : 1) + (has_skip ? Ns * elem : 0);
+  sh.rpc = 256 / sh.tpr;
+  while (sh.rpc > 1 && sh.rpc * row_bytes > 48 * 1024) sh.rpc /= 2;
+  if (sh.rpc < 1) sh.rpc = 1;
+  sh.stage_bytes = (sh.rpc * row_bytes + 127) / 128 * 128;
+  sh.stages = 64 * 1024 / sh.stage_bytes;
+  if (sh.stages < 2) sh.stages = 2;
+  if (sh.stages > kMaxStages) sh.stages = kMaxStages;
+  sh.smem = static_cast<size_t>(sh.stages) * sh.stage_bytes + (bwd ? static_cast<size_t>(2 * sh.rpc + 2) * N * sizeof(float) : 0);
+  return sh;
 }
 
 static int validate(const char* fn, const spectre_norm_act_t* d, bool bwd) {
@@ -389,35 +637,69 @@ static int validate(const char* fn, const spectre_norm_act_t* d, bool bwd) {
   if (!d->in0 || !d->gamma || !d->beta || !d->mean || !d->rstd) return fail(SPECTRE_E_NULL, "%s: null pointer", fn);
   if (d->rows < 1 || d->N < 8 || (d->N % 8) || d->N > 4096)
     return fail(SPECTRE_E_SHAPE, "%s: need rows >= 1 and N a multiple of 8 in [8, 4096] (rows=%lld N=%d)", fn, d->rows, d->N);
-  if (d->skip && (d->Ns < 1 || (d->Ns % 4)))
-    return fail(SPECTRE_E_SHAPE, "%s: skip width must be a positive multiple of 4 (Ns=%d)", fn, d->Ns);
-  if (d->in0_dtype != SPECTRE_DTYPE_F32 && d->in0_dtype != SPECTRE_DTYPE_BF16)
-    return fail(SPECTRE_E_DTYPE, "%s: in0_dtype=%d (0=float32, 1=bfloat16)", fn, d->in0_dtype);
+  const bool has_skip = bwd ? d->d_skip != nullptr : d->skip != nullptr;
+  if (has_skip && (d->Ns < 1 || (d->Ns % 8)))
+    return fail(SPECTRE_E_SHAPE, "%s: skip width must be a positive multiple of 8 (Ns=%d)", fn, d->Ns);
+  if (d->act_dtype != SPECTRE_DTYPE_F32 && d->act_dtype != SPECTRE_DTYPE_BF16)
+    return fail(SPECTRE_E_DTYPE, "%s: act_dtype=%d (0=float32, 1=bfloat16)", fn, d->act_dtype);
   if (d->drop_p < 0.f || d->drop_p >= 1.f) return fail(SPECTRE_E_SHAPE, "%s: drop_p=%g outside [0,1)", fn, d->drop_p);
-  const void* ptrs[] = {d->in0, d->in1, d->gamma, d->beta, d->skip, d->out, d->out_bf16, d->dout, d->dout_bf16,
-                        d->d_in0, d->d_in1, d->d_skip, d->dgamma, d->dbeta, d->workspace};
+  const void* ptrs[] = {d->in0, d->in1, d->gamma, d->beta, d->skip, d->out, d->dout,
+                        d->d_in0, d->d_skip, d->dgamma, d->dbeta, d->workspace};
   for (const void* q : ptrs)
     if (!aligned16(q)) return fail(SPECTRE_E_ALIGN, "%s: pointers must be 16-byte aligned", fn);
   if (!bwd && !d->out) return fail(SPECTRE_E_NULL, "%s: null out", fn);
-  if (bwd && (!d->dout || !d->dgamma || !d->dbeta || (d->skip && !d->d_skip) || (!d->d_in0 && !d->d_in1)))
-    return fail(SPECTRE_E_NULL, "%s: null gradient pointer", fn);
+  if (bwd && (!d->dout || !d->dgamma || !d->dbeta || !d->d_in0)) return fail(SPECTRE_E_NULL, "%s: null gradient pointer", fn);
   return SPECTRE_OK;
 }
 
-static Args to_args(const spectre_norm_act_t& d) {
+static Args to_args(const spectre_norm_act_t& d, bool bwd) {
   Args a{};
   a.in0 = d.in0; a.in1 = d.in1; a.gamma = d.gamma; a.beta = d.beta; a.skip = d.skip;
-  a.out = d.out; a.out_bf16 = d.out_bf16; a.mean = d.mean; a.rstd = d.rstd;
-  a.dout = d.dout; a.dout_bf16 = d.dout_bf16; a.d_in0 = d.d_in0; a.d_in1 = d.d_in1; a.d_skip = d.d_skip;
+  a.out = d.out; a.mean = d.mean; a.rstd = d.rstd;
+  a.dout = d.dout; a.d_in0 = d.d_in0; a.d_skip = d.d_skip;
   a.part = static_cast<float*>(d.workspace);
-  a.rows = d.rows; a.N = d.N; a.Ns = d.skip ? d.Ns : d.N; a.act = d.act; a.eps = d.eps; a.drop_p = d.drop_p; a.seed = d.seed;
-  pick_skip(d, &a.skip_mode, &a.k);
+  const bool has_skip = bwd ? d.d_skip != nullptr : d.skip != nullptr;
+  a.rows = d.rows; a.N = d.N; a.Ns = has_skip ? d.Ns : d.N; a.act = d.act; a.eps = d.eps; a.drop_p = d.drop_p;
+  a.seed_lo = static_cast<unsigned>(d.seed); a.seed_hi = static_cast<unsigned>(d.seed >> 32);
+  a.skip_mode = pick_skip(a.N, a.Ns, has_skip);
   return a;
 }
 
-static int bwd_grid(long long rows) {
-  const long long cap = static_cast<long long>(device_sm_count()) * 8;
-  return static_cast<int>(rows < cap ? rows : cap);
+static int grid_for(long long rows, const Shape& sh) {
+  const long long groups = (rows + sh.rpc - 1) / sh.rpc;
+  const int block = sh.tpr * sh.rpc;
+  int per_sm = 768 / block;                        // <= 3 CTAs of 256 threads (80 registers each)
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 6) per_sm = 6;
+  const int by_smem = static_cast<int>((220 * 1024) / (sh.smem + 1024));
+  if (per_sm > by_smem) per_sm = by_smem < 1 ? 1 : by_smem;
+  const long long cap = static_cast<long long>(device_sm_count()) * per_sm;
+  return static_cast<int>(groups < cap ? groups : cap);
+}
+
+// kernel table: [bf16][vpt - 1][mode]
+typedef void (*KernelFn)(const Args);
+template <class T, int VPT, int... M>
+static void fill_row(KernelFn* fwd, KernelFn* bwd, std::integer_sequence<int, M...>) {
+  ((fwd[M] = norm_act_fwd_kernel<T, VPT, M>, bwd[M] = norm_act_bwd_kernel<T, VPT, M>), ...);
+}
+struct KernelTable {
+  KernelFn fwd[2][2][kSkipModes], bwd[2][2][kSkipModes];
+  KernelTable() {
+    using Seq = std::make_integer_sequence<int, kSkipModes>;
+    fill_row<float, 1>(fwd[0][0], bwd[0][0], Seq{});
+    fill_row<float, 2>(fwd[0][1], bwd[0][1], Seq{});
+    fill_row<__nv_bfloat16, 1>(fwd[1][0], bwd[1][0], Seq{});
+    fill_row<__nv_bfloat16, 2>(fwd[1][1], bwd[1][1], Seq{});
+    for (auto& t : fwd) for (auto& v : t) for (KernelFn f : v)
+      cudaFuncSetAttribute(reinterpret_cast<const void*>(f), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    for (auto& t : bwd) for (auto& v : t) for (KernelFn f : v)
+      cudaFuncSetAttribute(reinterpret_cast<const void*>(f), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  }
+};
+static const KernelTable& table() {
+  static const KernelTable t;
+  return t;
 }
 
 }  // namespace na
@@ -430,20 +712,13 @@ extern "C" {
 
 int spectre_norm_act_fwd(const spectre_norm_act_t* d, void* stream) {
   if (int rc = validate("spectre_norm_act_fwd", d, false)) return rc;
-  const Args a = to_args(*d);
-  int vpt, block;
-  launch_shape(a.N, &vpt, &block);
-  const long long cap = static_cast<long long>(device_sm_count()) * 16;
-  const int grid = static_cast<int>(a.rows < cap ? a.rows : cap);
+  Args a = to_args(*d, false);
+  const bool bf = d->act_dtype == SPECTRE_DTYPE_BF16;
+  const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, a.skip_mode != kSkipNone, bf ? 2 : 4, false);
+  a.tpr = sh.tpr; a.rpc = sh.rpc; a.stages = sh.stages; a.stage_bytes = sh.stage_bytes;
+  const int grid = grid_for(a.rows, sh), block = sh.tpr * sh.rpc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const bool bf = d->in0_dtype == SPECTRE_DTYPE_BF16;
-  if (vpt == 1) {
-    if (bf) norm_act_fwd_kernel<__nv_bfloat16, 1><<<grid, block, 0, st>>>(a);
-    else norm_act_fwd_kernel<float, 1><<<grid, block, 0, st>>>(a);
-  } else {
-    if (bf) norm_act_fwd_kernel<__nv_bfloat16, 2><<<grid, block, 0, st>>>(a);
-    else norm_act_fwd_kernel<float, 2><<<grid, block, 0, st>>>(a);
-  }
+  table().fwd[bf ? 1 : 0][sh.vpt - 1][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
   last_launch_count() = 1;
   const cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "norm_act_fwd launch: %s", cudaGetErrorString(err));
@@ -451,36 +726,39 @@ int spectre_norm_act_fwd(const spectre_norm_act_t* d, void* stream) {
   return SPECTRE_OK;
 }
 
+// upper bound over both element types (the query has no dtype argument)
 size_t spectre_norm_act_bwd_workspace_bytes(long long rows, int N) {
   if (rows < 1 || N < 8) return 0;
-  return static_cast<size_t>(bwd_grid(rows)) * 2 * N * sizeof(float);
+  size_t best = 0;
+  for (int elem : {2, 4})
+    for (int in1 : {0, 1}) {
+      const Shape sh = launch_shape(N, N, in1 != 0, false, elem, true);
+      const size_t b = static_cast<size_t>(grid_for(rows, sh)) * 2 * N * sizeof(float);
+      if (b > best) best = b;
+    }
+  return best;
 }
 
 int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
   if (int rc = validate("spectre_norm_act_bwd", d, true)) return rc;
-  Args a = to_args(*d);
-  int vpt, block;
-  launch_shape(a.N, &vpt, &block);
-  const int grid = bwd_grid(a.rows);
+  Args a = to_args(*d, true);
+  const bool bf = d->act_dtype == SPECTRE_DTYPE_BF16;
+  const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, false, bf ? 2 : 4, true);
+  a.tpr = sh.tpr; a.rpc = sh.rpc; a.stages = sh.stages; a.stage_bytes = sh.stage_bytes;
+  const int grid = grid_for(a.rows, sh), block = sh.tpr * sh.rpc;
   if (!d->workspace || d->workspace_bytes < static_cast<size_t>(grid) * 2 * a.N * sizeof(float))
     return fail(SPECTRE_E_WORKSPACE, "spectre_norm_act_bwd: workspace %zu B < required %zu B", d->workspace_bytes,
                 static_cast<size_t>(grid) * 2 * a.N * sizeof(float));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const bool bf = d->in0_dtype == SPECTRE_DTYPE_BF16;
-  if (vpt == 1) {
-    if (bf) norm_act_bwd_kernel<__nv_bfloat16, 1><<<grid, block, 0, st>>>(a);
-    else norm_act_bwd_kernel<float, 1><<<grid, block, 0, st>>>(a);
-  } else {
-    if (bf) norm_act_bwd_kernel<__nv_bfloat16, 2><<<grid, block, 0, st>>>(a);
-    else norm_act_bwd_kernel<float, 2><<<grid, block, 0, st>>>(a);
-  }
+  table().bwd[bf ? 1 : 0][sh.vpt - 1][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
   int launches = 1;
   if (a.skip_mode == kSkipGeneral) {
     const long long n = a.rows * a.Ns;
-    pool_bwd_general_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a);
+    if (bf) pool_bwd_general_kernel<__nv_bfloat16><<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a);
+    else pool_bwd_general_kernel<float><<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a);
     ++launches;
   }
-  reduce_gamma_beta_kernel<<<(2 * a.N + 255) / 256, 256, 0, st>>>(a.part, d->dgamma, d->dbeta, a.N, grid);
+  reduce_gamma_beta_kernel<<<(2 * a.N + 31) / 32, 256, 0, st>>>(a.part, d->dgamma, d->dbeta, a.N, grid);
   ++launches;
   last_launch_count() = launches;
   const cudaError_t err = cudaGetLastError();

@@ -3,6 +3,10 @@
 
     out = dropout( act( LayerNorm(in0 + in1) * gamma + beta ) + adaptive_avg_pool(skip) )
 
+Every activation operand of a call has one dtype: float32, or bfloat16 for the bf16 training stream (the
+encoder keeps its residual stream in bf16 under bf16 autocast -- half the HBM traffic of autocast's
+fp32 LayerNorm outputs; statistics and arithmetic stay fp32).
+
 One CUDA pass each way replaces the LayerNorm / GELU / AdaptiveAvgPool1d / add / dropout launches of
 ``SpectreEncoderLayer.forward`` (``spectre_vit/models/spectre/spectre.py:65-73``) and
 ``SpectreLinear.forward`` (``spectre_vit/models/spectre/layers.py:95-101``).  CUDA only, no fallback:
@@ -25,11 +29,10 @@ def _ptr(t):
 
 
 class _NormAct(torch.autograd.Function):
-    """Returns ``(out_f32, out_bf16 or None)``; the bf16 twin is a second differentiable view of the same
-    values (its incoming gradient is added to ``out``'s inside the backward kernel)."""
+    """All activation operands share ``in0``'s dtype (float32, or bfloat16 for the bf16 stream)."""
 
     @staticmethod
-    def forward(ctx, in0, in1, skip, gamma, beta, eps, act, drop_p, seed, want_bf16):
+    def forward(ctx, in0, in1, skip, gamma, beta, eps, act, drop_p, seed):
         lib = _lib.load()
         if not in0.is_cuda:
             raise RuntimeError("norm_act: CUDA (sm_100a) only; there is no CPU fallback")
@@ -38,18 +41,17 @@ class _NormAct(torch.autograd.Function):
         N = in0.shape[-1]
         in0 = in0.contiguous()
         rows = in0.numel() // N
-        in1 = None if in1 is None else in1.float().contiguous()
-        skip = None if skip is None else skip.float().contiguous()
+        in1 = None if in1 is None else in1.to(in0.dtype).contiguous()
+        skip = None if skip is None else skip.to(in0.dtype).contiguous()
         gamma, beta = gamma.float().contiguous(), beta.float().contiguous()
-        out = torch.empty(in0.shape, dtype=torch.float32, device=in0.device)
-        out_bf16 = torch.empty(in0.shape, dtype=torch.bfloat16, device=in0.device) if want_bf16 else None
+        out = torch.empty_like(in0)
         mean = torch.empty(rows, dtype=torch.float32, device=in0.device)
         rstd = torch.empty_like(mean)
         d = _lib.NormActDesc()
         d.in0, d.in1, d.gamma, d.beta, d.skip = _ptr(in0), _ptr(in1), _ptr(gamma), _ptr(beta), _ptr(skip)
-        d.out, d.out_bf16, d.mean, d.rstd = _ptr(out), _ptr(out_bf16), _ptr(mean), _ptr(rstd)
+        d.out, d.mean, d.rstd = _ptr(out), _ptr(mean), _ptr(rstd)
         d.rows, d.N, d.Ns = rows, N, (skip.shape[-1] if skip is not None else N)
-        d.in0_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
+        d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
         with torch.cuda.device(in0.device):
             with _timed("norm_act_fwd", (rows, N, in0.element_size())):
                 rc = lib.spectre_norm_act_fwd(ctypes.byref(d), _stream_ptr(in0.device))
@@ -57,40 +59,26 @@ class _NormAct(torch.autograd.Function):
         _lib.count_launches()
         ctx.save_for_backward(in0, in1, gamma, beta, mean, rstd)
         ctx.meta = (skip.shape if skip is not None else None, float(eps), int(act), float(drop_p), int(seed))
-        ctx.need = (ctx.needs_input_grad[0], ctx.needs_input_grad[1] and in1 is not None)
-        if out_bf16 is None:
-            ctx.mark_non_differentiable()
-            return out, None
-        return out, out_bf16
+        return out
 
     @staticmethod
-    def backward(ctx, dout, dout_bf16):
+    def backward(ctx, dout):
         lib = _lib.load()
         in0, in1, gamma, beta, mean, rstd = ctx.saved_tensors
         skip_shape, eps, act, drop_p, seed = ctx.meta
         N = in0.shape[-1]
         rows = in0.numel() // N
         dev = in0.device
-        if dout is None:
-            dout = torch.zeros(in0.shape, dtype=torch.float32, device=dev)
-        dout = dout.float().contiguous()
-        if dout_bf16 is not None:
-            dout_bf16 = dout_bf16.to(torch.bfloat16).contiguous()
+        dout = dout.to(in0.dtype).contiguous()
         d_in0 = torch.empty_like(in0)
-        # in1 is float32; when in0 is float32 too both get the same tensor
-        d_in1 = None
-        if in1 is not None and in0.dtype != torch.float32:
-            d_in1 = torch.empty_like(in1)
-        d_skip = torch.empty(skip_shape, dtype=torch.float32, device=dev) if skip_shape is not None else None
+        d_skip = torch.empty(skip_shape, dtype=in0.dtype, device=dev) if skip_shape is not None else None
         dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(beta)
         d = _lib.NormActDesc()
         d.in0, d.in1, d.gamma, d.beta = _ptr(in0), _ptr(in1), _ptr(gamma), _ptr(beta)
-        # `skip` itself is not read by the backward; a non-null pointer only selects the pooling mode
-        d.skip = _ptr(d_skip)
-        d.mean, d.rstd, d.dout, d.dout_bf16 = _ptr(mean), _ptr(rstd), _ptr(dout), _ptr(dout_bf16)
-        d.d_in0, d.d_in1, d.d_skip, d.dgamma, d.dbeta = _ptr(d_in0), _ptr(d_in1), _ptr(d_skip), _ptr(dgamma), _ptr(dbeta)
+        d.mean, d.rstd, d.dout = _ptr(mean), _ptr(rstd), _ptr(dout)
+        d.d_in0, d.d_skip, d.dgamma, d.dbeta = _ptr(d_in0), _ptr(d_skip), _ptr(dgamma), _ptr(dbeta)
         d.rows, d.N, d.Ns = rows, N, (skip_shape[-1] if skip_shape is not None else N)
-        d.in0_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], act, eps, drop_p, seed
+        d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], act, eps, drop_p, seed
         with torch.cuda.device(dev):
             nws = lib.spectre_norm_act_bwd_workspace_bytes(rows, N)
             ws = torch.empty(max(nws, 16), dtype=torch.uint8, device=dev)
@@ -99,16 +87,14 @@ class _NormAct(torch.autograd.Function):
                 rc = lib.spectre_norm_act_bwd(ctypes.byref(d), _stream_ptr(dev))
         _lib.check(rc, "spectre_norm_act_bwd")
         _lib.count_launches()
-        g_in1 = None
-        if in1 is not None:
-            g_in1 = d_in0 if d_in1 is None else d_in1
-        return d_in0, g_in1, d_skip, dgamma, dbeta, None, None, None, None, None
+        # d(in0 + in1): the same values for both addends
+        return d_in0, (d_in0 if in1 is not None else None), d_skip, dgamma, dbeta, None, None, None, None
 
 
-def norm_act(in0, gamma, beta, *, in1=None, skip=None, eps=1e-5, act="none", drop_p=0.0, seed=0, want_bf16=False):
+def norm_act(in0, gamma, beta, *, in1=None, skip=None, eps=1e-5, act="none", drop_p=0.0, seed=0):
     """``dropout(act(LayerNorm(in0 + in1) * gamma + beta) + adaptive_avg_pool(skip))`` in one CUDA pass.
 
-    in0 ``[..., N]`` float32 / bfloat16; in1 ``[..., N]``, skip ``[..., Ns]`` float32 (or None).
-    Returns ``(out_float32, out_bfloat16 | None)``.
+    in0 ``[..., N]`` float32 / bfloat16; in1 ``[..., N]``, skip ``[..., Ns]`` (cast to in0's dtype if they
+    differ).  Returns ``out`` in in0's dtype; statistics and arithmetic are float32.
     """
-    return _NormAct.apply(in0, in1, skip, gamma, beta, eps, 1 if act == "gelu" else 0, drop_p, seed, want_bf16)
+    return _NormAct.apply(in0, in1, skip, gamma, beta, eps, 1 if act == "gelu" else 0, drop_p, seed)

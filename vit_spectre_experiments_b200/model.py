@@ -119,36 +119,37 @@ class SpectreEncoderLayer(nn.Module):
         return self.dropout2(self.linear3(self.dropout1(self.linear1(x))))
 
     def use_fused(self, x: torch.Tensor) -> bool:
-        if not (self.fused and self._fusable and x.is_cuda and x.dtype == torch.float32):
+        if not (self.fused and self._fusable and x.is_cuda and x.dtype in (torch.float32, torch.bfloat16)):
             return False
         return not torch.is_autocast_enabled() or torch.get_autocast_dtype("cuda") == torch.bfloat16
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.use_fused(x):
-            return self.forward_fused(x, None)[0]
+            return self.forward_fused(x).to(x.dtype)
         x = self.norm1(self.mix_layer(x)) + x
         return self.norm2(x + self._ff_block(x))
 
-    def forward_fused(self, x: torch.Tensor, x_bf16):
-        """Same arithmetic through the fused kernels.  ``x_bf16`` is an optional bf16 twin of ``x`` (written
-        by the previous layer's last kernel) that feeds the bf16 mixer without a cast pass; returns
-        ``(x2_float32, x2_bfloat16 | None)``."""
+    def forward_fused(self, x: torch.Tensor) -> torch.Tensor:
+        """Same arithmetic through the fused kernels.  Under bf16 autocast the residual stream is bf16 from
+        end to end (one cast at the encoder entry; every kernel reads and writes bf16, statistics fp32);
+        otherwise everything stays float32.  Returns the layer output in the stream dtype."""
         from .fused import norm_act
 
-        twin = torch.is_autocast_enabled()
-        m = self.mix_layer(x_bf16 if (twin and x_bf16 is not None) else x)
-        x1, x1b = norm_act(m, self.norm1.weight, self.norm1.bias, skip=x, eps=self.norm1.eps, want_bf16=twin)
+        if torch.is_autocast_enabled() and x.dtype != torch.bfloat16:
+            x = x.to(torch.bfloat16)
+        m = self.mix_layer(x)
+        x1 = norm_act(m, self.norm1.weight, self.norm1.bias, skip=x, eps=self.norm1.eps)
         lin1, ln1 = self.linear1.local_head[0], self.linear1.local_head[1]
         lin3, ln3 = self.linear3.local_head[0], self.linear3.local_head[1]
         p1 = self.dropout1.p if self.training else 0.0
         p2 = self.dropout2.p if self.training else 0.0
-        h1 = F.linear(x1b if x1b is not None else x1, lin1.weight, lin1.bias)
-        a1, a1b = norm_act(h1, ln1.weight, ln1.bias, skip=x1, eps=ln1.eps, act="gelu", drop_p=p1,
-                           seed=_dropout_seed() if p1 > 0 else 0, want_bf16=twin)
-        h2 = F.linear(a1b if a1b is not None else a1, lin3.weight, lin3.bias)
-        ff, _ = norm_act(h2, ln3.weight, ln3.bias, skip=a1, eps=ln3.eps, act="gelu", drop_p=p2,
-                         seed=_dropout_seed() if p2 > 0 else 0)
-        return norm_act(x1, self.norm2.weight, self.norm2.bias, in1=ff, eps=self.norm2.eps, want_bf16=twin)
+        h1 = F.linear(x1, lin1.weight, lin1.bias)
+        a1 = norm_act(h1, ln1.weight, ln1.bias, skip=x1, eps=ln1.eps, act="gelu", drop_p=p1,
+                      seed=_dropout_seed() if p1 > 0 else 0)
+        h2 = F.linear(a1, lin3.weight, lin3.bias)
+        ff = norm_act(h2, ln3.weight, ln3.bias, skip=a1, eps=ln3.eps, act="gelu", drop_p=p2,
+                      seed=_dropout_seed() if p2 > 0 else 0)
+        return norm_act(x1, self.norm2.weight, self.norm2.bias, in1=ff, eps=self.norm2.eps)
 
 
 class SpectreEncoder(nn.Module):
@@ -164,9 +165,9 @@ class SpectreEncoder(nn.Module):
     def forward(self, src: torch.Tensor) -> torch.Tensor:
         out = src
         if all(isinstance(l, SpectreEncoderLayer) and l.use_fused(src) for l in self.layers):
-            twin = None   # bf16 copy of `out`, handed from layer to layer under autocast
-            for layer in self.layers:
-                out, twin = layer.forward_fused(out, twin)
+            for layer in self.layers:   # bf16 stream under bf16 autocast, fp32 otherwise
+                out = layer.forward_fused(out)
+            out = out.to(src.dtype)
         else:
             for layer in self.layers:
                 out = layer(out)
