@@ -262,7 +262,7 @@ __device__ __forceinline__ void skip_down_bwd(T* drow, int j0, const float (&d)[
 }
 
 // ------------------------------------------------------------------ forward
-template <class T, int VPT, int MODE>
+template <class T, int VPT, int MODE, int ACT>
 __global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
   extern __shared__ __align__(128) uint8_t ring[];
   __shared__ uint64_t full[kMaxStages];
@@ -359,7 +359,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           const float u = fmaf(fmaf(z[i][e], rstd, shift), g[e], b[e]);
-          o[e] = a.act ? gelu(u) : u;
+          o[e] = ACT ? gelu(u) : u;
         }
         if constexpr (MODE == kSkipIdentity) {
           float sk[8];
@@ -389,7 +389,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
 
 // ------------------------------------------------------------------ backward
 // d = dout * dropout_mask ; d_skip = pool^T(d) ; g = d * act'(u) ; LayerNorm backward of g.
-template <class T, int VPT, int MODE>
+template <class T, int VPT, int MODE, int ACT>
 __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   extern __shared__ __align__(128) uint8_t ring[];
   __shared__ uint64_t full[kMaxStages];
@@ -491,7 +491,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
       // ---- main path
       float gam[8], bet[8], dg[8], db[8];
       ld8(sgam + j0, gam);
-      if (a.act) ld8(sgam + a.N + j0, bet);
+      if (ACT) ld8(sgam + a.N + j0, bet);
       ld8(myacc + j0, dg);
       ld8(myacc + a.N + j0, db);
       float s0 = 0.f, s1 = 0.f;
@@ -499,7 +499,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
       for (int e = 0; e < 8; ++e) {
         const float x = fmaf(z[e], rstd, shift);
         float g = d[e];
-        if (a.act) g *= gelu_grad(fmaf(x, gam[e], bet[e]));
+        if (ACT) g *= gelu_grad(fmaf(x, gam[e], bet[e]));
         db[e] += g;
         dg[e] = fmaf(g, x, dg[e]);
         const float y = g * gam[e];
@@ -625,7 +625,7 @@ static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, 
   while (sh.rpc > 1 && sh.rpc * row_bytes > 48 * 1024) sh.rpc /= 2;
   if (sh.rpc < 1) sh.rpc = 1;
   sh.stage_bytes = (sh.rpc * row_bytes + 127) / 128 * 128;
-  sh.stages = 64 * 1024 / sh.stage_bytes;
+  sh.stages = (bwd ? 36 : 64) * 1024 / sh.stage_bytes;
   if (sh.stages < 2) sh.stages = 2;
   if (sh.stages > kMaxStages) sh.stages = kMaxStages;
   sh.smem = static_cast<size_t>(sh.stages) * sh.stage_bytes + (bwd ? static_cast<size_t>(2 * sh.rpc + 2) * N * sizeof(float) : 0);
@@ -677,23 +677,27 @@ static int grid_for(long long rows, const Shape& sh) {
   return static_cast<int>(groups < cap ? groups : cap);
 }
 
-// kernel table: [bf16][vpt - 1][mode]
+// kernel table: [bf16][vpt - 1][act][mode]
 typedef void (*KernelFn)(const Args);
-template <class T, int VPT, int... M>
+template <class T, int VPT, int ACT, int... M>
 static void fill_row(KernelFn* fwd, KernelFn* bwd, std::integer_sequence<int, M...>) {
-  ((fwd[M] = norm_act_fwd_kernel<T, VPT, M>, bwd[M] = norm_act_bwd_kernel<T, VPT, M>), ...);
+  ((fwd[M] = norm_act_fwd_kernel<T, VPT, M, ACT>, bwd[M] = norm_act_bwd_kernel<T, VPT, M, ACT>), ...);
 }
 struct KernelTable {
-  KernelFn fwd[2][2][kSkipModes], bwd[2][2][kSkipModes];
+  KernelFn fwd[2][2][2][kSkipModes], bwd[2][2][2][kSkipModes];
   KernelTable() {
     using Seq = std::make_integer_sequence<int, kSkipModes>;
-    fill_row<float, 1>(fwd[0][0], bwd[0][0], Seq{});
-    fill_row<float, 2>(fwd[0][1], bwd[0][1], Seq{});
-    fill_row<__nv_bfloat16, 1>(fwd[1][0], bwd[1][0], Seq{});
-    fill_row<__nv_bfloat16, 2>(fwd[1][1], bwd[1][1], Seq{});
-    for (auto& t : fwd) for (auto& v : t) for (KernelFn f : v)
+    fill_row<float, 1, 0>(fwd[0][0][0], bwd[0][0][0], Seq{});
+    fill_row<float, 1, 1>(fwd[0][0][1], bwd[0][0][1], Seq{});
+    fill_row<float, 2, 0>(fwd[0][1][0], bwd[0][1][0], Seq{});
+    fill_row<float, 2, 1>(fwd[0][1][1], bwd[0][1][1], Seq{});
+    fill_row<__nv_bfloat16, 1, 0>(fwd[1][0][0], bwd[1][0][0], Seq{});
+    fill_row<__nv_bfloat16, 1, 1>(fwd[1][0][1], bwd[1][0][1], Seq{});
+    fill_row<__nv_bfloat16, 2, 0>(fwd[1][1][0], bwd[1][1][0], Seq{});
+    fill_row<__nv_bfloat16, 2, 1>(fwd[1][1][1], bwd[1][1][1], Seq{});
+    for (auto& t : fwd) for (auto& v : t) for (auto& w : v) for (KernelFn f : w)
       cudaFuncSetAttribute(reinterpret_cast<const void*>(f), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    for (auto& t : bwd) for (auto& v : t) for (KernelFn f : v)
+    for (auto& t : bwd) for (auto& v : t) for (auto& w : v) for (KernelFn f : w)
       cudaFuncSetAttribute(reinterpret_cast<const void*>(f), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   }
 };
@@ -718,7 +722,7 @@ int spectre_norm_act_fwd(const spectre_norm_act_t* d, void* stream) {
   a.tpr = sh.tpr; a.rpc = sh.rpc; a.stages = sh.stages; a.stage_bytes = sh.stage_bytes;
   const int grid = grid_for(a.rows, sh), block = sh.tpr * sh.rpc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  table().fwd[bf ? 1 : 0][sh.vpt - 1][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
+  table().fwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
   last_launch_count() = 1;
   const cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "norm_act_fwd launch: %s", cudaGetErrorString(err));
@@ -750,7 +754,7 @@ int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
     return fail(SPECTRE_E_WORKSPACE, "spectre_norm_act_bwd: workspace %zu B < required %zu B", d->workspace_bytes,
                 static_cast<size_t>(grid) * 2 * a.N * sizeof(float));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  table().bwd[bf ? 1 : 0][sh.vpt - 1][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
+  table().bwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
   int launches = 1;
   if (a.skip_mode == kSkipGeneral) {
     const long long n = a.rows * a.Ns;
