@@ -186,7 +186,9 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sOut = smem + SM::kOut;
   uint8_t* sMat = smem + SM::kMat;
-  __shared__ uint64_t full_bar[S], empty_bar[S], dready_bar[4];
+  // dready_bar[stage][sub]: every stage's MMAs are committed in up to four sub-batches so the epilogue of the
+  // first batch overlaps the issue / execution of the rest (the issuing thread needs ~50 clk per MMA)
+  __shared__ uint64_t full_bar[S], empty_bar[S], dready_bar[4][4];
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) uint8_t sDummy[8 * 16];   // sink for the padded rows of stmatrix
 
@@ -204,7 +206,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     prefetch_tensormap(&tmap_x);
     prefetch_tensormap(&tmap_y);
     for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int k = 0; k < 4; ++k) mbar_init(&dready_bar[k], 1);
+    for (int k = 0; k < 16; ++k) mbar_init(&dready_bar[k >> 2][k & 3], 1);
     mbar_fence_init();
     // prologue loads: fill the input ring before the CTA-wide setup barrier (only the barriers are needed)
     const uint32_t bytes0 = (half1 ? 2u : 1u) * C::HW * 128u;
@@ -291,13 +293,16 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
       const int b = img0 + it * p.img_stride;
       // ---------------- E1: D1[h][slot,ri] -> A2[kw][h] (bf16 pairs)
       if (stamp) SB200_STAMP(g, it, 0);
-      mbar_wait(&dready_bar[0], par);
-      tc_fence_after_sync();
-      if (stamp) SB200_STAMP(g, it, 1);
       {
-        // A2C is a multiple of 4: each batch of 4 grid rows becomes one 4-column store per kw
+        // A2C is a multiple of 4: each batch of 4 grid rows becomes one 4-column store per kw; batch hb / 4 of
+        // the row MMAs has its own commit barrier
 #pragma unroll
         for (int hb = 0; hb < A2C; hb += 4) {
+          if (hb < H) {
+            mbar_wait(&dready_bar[0][hb >> 2], par);
+            tc_fence_after_sync();
+          }
+          if (hb == 0 && stamp) SB200_STAMP(g, it, 1);
           uint32_t v[4][8];
 #pragma unroll
           for (int i = 0; i < 4; ++i)
@@ -319,14 +324,15 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
       }
       if (stamp) SB200_STAMP(g, it, 2);
       // ---------------- E2: Z = D2 * filter -> A3[kw][kh]   (loads double-buffered)
-      mbar_wait(&dready_bar[1], par);
-      tc_fence_after_sync();
-      if (stamp) SB200_STAMP(g, it, 3);
       {
-        // 16-column units (8 complex bins), double-buffered: unit u = (kw_local, half)
+        // 16-column units (8 complex bins), double-buffered: unit u = (kw_local, half); the MMAs of local
+        // column j (of both warpgroups) are committed on dready_bar[1][j]
         constexpr int UPK = K2 / 16, NU = KWG * UPK;
         uint32_t v[2][16];
         uint32_t ft[16];
+        mbar_wait(&dready_bar[1][0], par);
+        tc_fence_after_sync();
+        if (stamp) SB200_STAMP(g, it, 3);
         if (g * KWG < WH) tmem_ld16(tD + (g * KWG) * K2, v[0]);
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
@@ -334,7 +340,12 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
           const int kw = g * KWG + j;
           tmem_wait_ld();
           if (u + 1 < NU) {
-            const int kwn = g * KWG + (u + 1) / UPK;
+            const int jn = (u + 1) / UPK;
+            const int kwn = g * KWG + jn;
+            if (jn != j) {
+              mbar_wait(&dready_bar[1][jn], par);
+              tc_fence_after_sync();
+            }
             if (kwn < WH) {
               tmem_ld16(tD + kwn * K2 + ((u + 1) % UPK) * 16, v[(u + 1) & 1]);
               if ((u + 1) % UPK == 1) tmem_ld16(tF + ((u + 1) / UPK) * 16, ft);
@@ -362,11 +373,12 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
       named_bar_arrive(2, kBarCount);
       if (stamp) SB200_STAMP(g, it, 4);
       // ---------------- E3: D3[kw][h,ri] -> A4[h][slot]
-      mbar_wait(&dready_bar[2], par);
-      tc_fence_after_sync();
-      if (stamp) SB200_STAMP(g, it, 5);
       {
-        // two kw columns at a time: their (re, im) pairs go to adjacent K slots of every grid row
+        // two kw columns at a time: their (re, im) pairs go to adjacent K slots of every grid row.  No sub-batches
+        // here: A4 [h][slot] overlays the A3 [kw] operands, so every inverse-column MMA must have completed.
+        mbar_wait(&dready_bar[2][0], par);
+        tc_fence_after_sync();
+        if (stamp) SB200_STAMP(g, it, 5);
 #pragma unroll
         for (int jp = 0; jp < 4; jp += 2) {
           const int kw0 = g * KWG + jp, kw1 = kw0 + 1;
@@ -387,7 +399,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
       if (stamp) SB200_STAMP(g, it, 6);
       // ---------------- E4: D4[h][w] -> bf16 -> swizzled smem tile -> TMA store
       if (tid == 0) tma_store_wait_read<0>();          // previous tile's store has drained sOut
-      mbar_wait(&dready_bar[3], par);
+      mbar_wait(&dready_bar[3][0], par);               // rows i of both warpgroups: sub-batch i / 2
       tc_fence_after_sync();
       if (stamp) SB200_STAMP(g, it, 7);
       {
@@ -415,6 +427,10 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             if (h0 + i < H) {
               tmem_wait_ld();
               if (i + 1 < HG && h0 + i + 1 < H) {
+                if (((i + 1) & 1) == 0) {
+                  mbar_wait(&dready_bar[3][(i + 1) >> 1], par);
+                  tc_fence_after_sync();
+                }
                 tmem_ld_16x256b_x2(tD + (h0 + i + 1) * 16, a[(i + 1) & 1]);
                 tmem_ld_16x256b_x2(tD + (16u << 16) + (h0 + i + 1) * 16, bq[(i + 1) & 1]);
               }
@@ -470,9 +486,11 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         if (elect_one()) {
           const uint64_t a0 = umma_smem_desc(smem_u32(smem + s * C::kStageBytes), C::kHalfStride, 1024, kSwz128);
 #pragma unroll
-          for (int h = 0; h < H; ++h) umma_ss(tD + h * 16, a0 + static_cast<uint64_t>(h * W * 8), b1, id_row, 0);
+          for (int h = 0; h < H; ++h) {
+            umma_ss(tD + h * 16, a0 + static_cast<uint64_t>(h * W * 8), b1, id_row, 0);
+            if ((h & 3) == 3 || h == H - 1) umma_commit(&dready_bar[0][h >> 2]);
+          }
           umma_commit(&empty_bar[s]);
-          umma_commit(&dready_bar[0]);
         }
         __syncwarp();
         if (lane == 0) SB200_STAMP(2, it, 2);
@@ -480,12 +498,20 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         tc_fence_after_sync();
         if (lane == 0) SB200_STAMP(2, it, 3);
         if (elect_one()) {
+          // local column j of warpgroup 0 (kw = j) and of warpgroup 1 (kw = KWG + j), then one commit
 #pragma unroll
-          for (int kw = 0; kw < WH; ++kw)
+          for (int j = 0; j < KWG; ++j) {
 #pragma unroll
-            for (int ks = 0; ks < K2 / 16; ++ks)
-              umma_ts(tD + kw * K2, tA + kw * A2C + ks * 8, b2 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
-          umma_commit(&dready_bar[1]);
+            for (int g2 = 0; g2 < 2; ++g2) {
+              const int kw = g2 * KWG + j;
+              if (kw < WH) {
+#pragma unroll
+                for (int ks = 0; ks < K2 / 16; ++ks)
+                  umma_ts(tD + kw * K2, tA + kw * A2C + ks * 8, b2 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
+              }
+            }
+            umma_commit(&dready_bar[1][j]);
+          }
         }
         __syncwarp();
         if (lane == 0) SB200_STAMP(2, it, 4);
@@ -498,7 +524,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 #pragma unroll
             for (int ks = 0; ks < K2 / 16; ++ks)
               umma_ts(tD + kw * K2, tA + kw * A2C + ks * 8, b3 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
-          umma_commit(&dready_bar[2]);
+          umma_commit(&dready_bar[2][0]);
         }
         __syncwarp();
         if (lane == 0) SB200_STAMP(2, it, 6);
@@ -506,9 +532,13 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         tc_fence_after_sync();
         if (lane == 0) SB200_STAMP(2, it, 7);
         if (elect_one()) {
+          // grid rows i of both warpgroups (h = i and h = HG + i); one commit per two i
 #pragma unroll
-          for (int h = 0; h < H; ++h) umma_ts(tD + h * 16, tA + h * 8, b4, id_irow, 0);
-          umma_commit(&dready_bar[3]);
+          for (int i = 0; i < HG; ++i) {
+            umma_ts(tD + i * 16, tA + i * 8, b4, id_irow, 0);
+            if (HG + i < H) umma_ts(tD + (HG + i) * 16, tA + (HG + i) * 8, b4, id_irow, 0);
+            if ((i & 1) == 1 || i == HG - 1) umma_commit(&dready_bar[3][i >> 1]);
+          }
         }
         __syncwarp();
         if (lane == 0) SB200_STAMP(2, it, 8);
@@ -652,12 +682,17 @@ struct BwdParams {
   long long* prof;
 };
 
-// E1 (shared by dy and x): D1[h][slot,ri] (fp32) -> bf16 A operand [slot][h] at tAdst, 4 grid rows per store
+// E1 (shared by dy and x): D1[h][slot,ri] (fp32) -> bf16 A operand [slot][h] at tAdst, 4 grid rows per store;
+// batch hb / 4 of the row MMAs is committed on bars[hb / 4]
 template <class C>
-__device__ __forceinline__ void epi_rows_to_cols(uint32_t tD, uint32_t tAdst, int g) {
+__device__ __forceinline__ void epi_rows_to_cols(uint32_t tD, uint32_t tAdst, int g, uint64_t* bars, uint32_t par) {
   constexpr int H = C::H, A2C = C::A2C;
 #pragma unroll
   for (int hb = 0; hb < A2C; hb += 4) {
+    if (hb < H) {
+      mbar_wait(&bars[hb >> 2], par);
+      tc_fence_after_sync();
+    }
     uint32_t v[4][8];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -689,7 +724,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
   uint8_t* sOut = smem + SM::kOut;
   float* sF = reinterpret_cast<float*>(smem + SM::kFilt);
   uint8_t* sMat = smem + SM::kMat;
-  __shared__ uint64_t full_bar[2], empty_bar[2], dready_bar[6];
+  __shared__ uint64_t full_bar[2], empty_bar[2], dready_bar[6][4];   // [phase][sub-batch], see the forward kernel
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) uint8_t sDummy[8 * 16];
 
@@ -711,7 +746,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
     prefetch_tensormap(&tmap_x);
     prefetch_tensormap(&tmap_dx);
     for (int s = 0; s < 2; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int k = 0; k < 6; ++k) mbar_init(&dready_bar[k], 1);
+    for (int k = 0; k < 24; ++k) mbar_init(&dready_bar[k >> 2][k & 3], 1);
     mbar_fence_init();
     if (ntiles > 0) {   // prologue: first tile's dy and x
       const int b0 = 2 * pair0;
@@ -807,31 +842,27 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
       const bool mvalid = m < 64 || two;
       // ---------------- rows(dy) -> A_dy ; rows(x) -> A_x
       if (stamp) SB200_STAMP(g, it, 0);
-      mbar_wait(&dready_bar[0], par);
-      tc_fence_after_sync();
-      if (stamp) SB200_STAMP(g, it, 1);
-      epi_rows_to_cols<C>(tD, tADy, g);
+      epi_rows_to_cols<C>(tD, tADy, g, dready_bar[0], par);
       tc_fence_before_sync();
       named_bar_arrive(1, kBarCount);
       if (stamp) SB200_STAMP(g, it, 2);
-      mbar_wait(&dready_bar[1], par);
-      tc_fence_after_sync();
-      if (stamp) SB200_STAMP(g, it, 3);
-      epi_rows_to_cols<C>(tD, tAX, g);
+      epi_rows_to_cols<C>(tD, tAX, g, dready_bar[1], par);
       tc_fence_before_sync();
       named_bar_arrive(2, kBarCount);
       if (stamp) SB200_STAMP(g, it, 4);
       // ---------------- cols: acc += conj(X) * DY ;  Z = conj(filt) * DY -> A_dy
 #pragma unroll
       for (int hf = 0; hf < 2; ++hf) {
-        mbar_wait(&dready_bar[2 + hf], par);
-        tc_fence_after_sync();
-        if (stamp) SB200_STAMP(g, it, 5 + 2 * hf);
         constexpr int NU = 2 * UPK;                            // units: (e, half of the kh range)
         const bool live0 = kw_of(4 * hf + 2 * g) >= 0, live1 = kw_of(4 * hf + 2 * g + 1) >= 0;
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
           const int e = u / UPK, hk = u % UPK;
+          if (hk == 0) {                                       // local slot e of both warpgroups: sub-batch e
+            mbar_wait(&dready_bar[2 + hf][e], par);
+            tc_fence_after_sync();
+            if (e == 0 && stamp) SB200_STAMP(g, it, 5 + 2 * hf);
+          }
           const bool live = e == 0 ? live0 : live1;
           if (live) {
             const int s = 4 * hf + 2 * g + e;
@@ -873,11 +904,11 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
         if (stamp) SB200_STAMP(g, it, 6 + 2 * hf);
       }
       // ---------------- cols^-1: D3[slot][h,ri] -> A4[h][slot] (in the A_x region)
-      mbar_wait(&dready_bar[4], par);
-      tc_fence_after_sync();
-      if (stamp) SB200_STAMP(g, it, 9);
 #pragma unroll
       for (int jp = 0; jp < 4; jp += 2) {
+        mbar_wait(&dready_bar[4][jp >> 1], par);               // slot pair jp of both warpgroups
+        tc_fence_after_sync();
+        if (jp == 0 && stamp) SB200_STAMP(g, it, 9);
         const int s0 = 4 * g + jp, s1 = s0 + 1;
         const bool live0 = kw_of(s0) >= 0, live1 = kw_of(s1) >= 0;
         uint32_t v0[K2], v1[K2];
@@ -895,7 +926,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
       if (stamp) SB200_STAMP(g, it, 10);
       // ---------------- rows^-1: D4[h][w] -> bf16 -> swizzled smem tile -> TMA store of dx
       if (tid == 0) tma_store_wait_read<0>();
-      mbar_wait(&dready_bar[5], par);
+      mbar_wait(&dready_bar[5][0], par);
       tc_fence_after_sync();
       if (stamp) SB200_STAMP(g, it, 11);
       {
@@ -919,6 +950,10 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
             if (h0 + i < H) {
               tmem_wait_ld();
               if (i + 1 < HG && h0 + i + 1 < H) {
+                if (((i + 1) & 1) == 0) {
+                  mbar_wait(&dready_bar[5][(i + 1) >> 1], par);
+                  tc_fence_after_sync();
+                }
                 tmem_ld_16x256b_x2(tD + (h0 + i + 1) * 16, a[(i + 1) & 1]);
                 tmem_ld_16x256b_x2(tD + (16u << 16) + (h0 + i + 1) * 16, bq[(i + 1) & 1]);
               }
@@ -1017,9 +1052,11 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
         if (lane == 0) SB200_STAMP(2, it, 1);
         if (elect_one()) {
 #pragma unroll
-          for (int h = 0; h < H; ++h) umma_ss(tD + h * 16, a_dy + static_cast<uint64_t>(h * W * 8), b1, id_row, 0);
+          for (int h = 0; h < H; ++h) {
+            umma_ss(tD + h * 16, a_dy + static_cast<uint64_t>(h * W * 8), b1, id_row, 0);
+            if ((h & 3) == 3 || h == H - 1) umma_commit(&dready_bar[0][h >> 2]);
+          }
           umma_commit(&empty_bar[0]);
-          umma_commit(&dready_bar[0]);
         }
         __syncwarp();
         mbar_wait(&full_bar[1], par);
@@ -1028,9 +1065,11 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
         if (lane == 0) SB200_STAMP(2, it, 2);
         if (elect_one()) {
 #pragma unroll
-          for (int h = 0; h < H; ++h) umma_ss(tD + h * 16, a_x + static_cast<uint64_t>(h * W * 8), b1, id_row, 0);
+          for (int h = 0; h < H; ++h) {
+            umma_ss(tD + h * 16, a_x + static_cast<uint64_t>(h * W * 8), b1, id_row, 0);
+            if ((h & 3) == 3 || h == H - 1) umma_commit(&dready_bar[1][h >> 2]);
+          }
           umma_commit(&empty_bar[1]);
-          umma_commit(&dready_bar[1]);
         }
         __syncwarp();
 #pragma unroll
@@ -1039,17 +1078,22 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
           tc_fence_after_sync();
           if (lane == 0) SB200_STAMP(2, it, 3 + hf);
           if (elect_one()) {
+            // local slot e of warpgroup 0 (sl = e) and of warpgroup 1 (sl = 2 + e), then one commit
 #pragma unroll
-            for (int sl = 0; sl < 4; ++sl) {
-              if (C::kw_of_slot(4 * hf + sl) >= 0) {
+            for (int e = 0; e < 2; ++e) {
 #pragma unroll
-                for (int ks = 0; ks < K2 / 16; ++ks) {
-                  umma_ts(tD + sl * K2, tADy + (4 * hf + sl) * A2C + ks * 8, b2 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
-                  umma_ts(tD + 128 + sl * K2, tAX + (4 * hf + sl) * A2C + ks * 8, b2 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
+              for (int g2 = 0; g2 < 2; ++g2) {
+                const int sl = 2 * g2 + e;
+                if (C::kw_of_slot(4 * hf + sl) >= 0) {
+#pragma unroll
+                  for (int ks = 0; ks < K2 / 16; ++ks) {
+                    umma_ts(tD + sl * K2, tADy + (4 * hf + sl) * A2C + ks * 8, b2 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
+                    umma_ts(tD + 128 + sl * K2, tAX + (4 * hf + sl) * A2C + ks * 8, b2 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
+                  }
                 }
               }
+              umma_commit(&dready_bar[2 + hf][e]);
             }
-            umma_commit(&dready_bar[2 + hf]);
           }
           __syncwarp();
         }
@@ -1057,15 +1101,22 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
         tc_fence_after_sync();
         if (lane == 0) SB200_STAMP(2, it, 5);
         if (elect_one()) {
+          // slot pair jp of warpgroup 0 (s = jp, jp+1) and of warpgroup 1 (s = 4+jp, 5+jp), then one commit
 #pragma unroll
-          for (int s = 0; s < 8; ++s) {
-            if (C::kw_of_slot(s) >= 0) {
+          for (int jp = 0; jp < 4; jp += 2) {
 #pragma unroll
-              for (int ks = 0; ks < K2 / 16; ++ks)
-                umma_ts(tD + s * K2, tADy + s * A2C + ks * 8, b3 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
-            }
+            for (int g2 = 0; g2 < 2; ++g2)
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const int sl = 4 * g2 + jp + e;
+                if (C::kw_of_slot(sl) >= 0) {
+#pragma unroll
+                  for (int ks = 0; ks < K2 / 16; ++ks)
+                    umma_ts(tD + sl * K2, tADy + sl * A2C + ks * 8, b3 + static_cast<uint64_t>(ks * 16), id_col, ks > 0);
+                }
+              }
+            umma_commit(&dready_bar[4][jp >> 1]);
           }
-          umma_commit(&dready_bar[4]);
         }
         __syncwarp();
         named_bar_sync(5, kBarCount);
@@ -1073,8 +1124,11 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
         if (lane == 0) SB200_STAMP(2, it, 6);
         if (elect_one()) {
 #pragma unroll
-          for (int h = 0; h < H; ++h) umma_ts(tD + h * 16, tAX + h * 8, b4, id_irow, 0);
-          umma_commit(&dready_bar[5]);
+          for (int i = 0; i < HG; ++i) {
+            umma_ts(tD + i * 16, tAX + i * 8, b4, id_irow, 0);
+            if (HG + i < H) umma_ts(tD + (HG + i) * 16, tAX + (HG + i) * 8, b4, id_irow, 0);
+            if ((i & 1) == 1 || i == HG - 1) umma_commit(&dready_bar[5][i >> 1]);
+          }
         }
         __syncwarp();
         if (lane == 0) SB200_STAMP(2, it, 7);
