@@ -101,8 +101,9 @@ size_t spectre_dwtmix_bwd_workspace_bytes(int B, int H, int W, int E);
 typedef struct spectre_norm_act_t {
   const void* in0; const void* in1; const float* gamma; const float* beta; const void* skip;
   void* out; float* mean; float* rstd;
-  const void* dout;
+  const void* dout; const void* dout2 /* optional second addend of the upstream gradient */;
   void* d_in0; void* d_skip; float* dgamma; float* dbeta;
+  float* dcolsum /* optional [N]: column sums of d_in0 = bias gradient of the Linear that produced in0 */;
   void* workspace; size_t workspace_bytes;
   long long rows; int N; int Ns; int act_dtype; int act /* 0 identity, 1 GELU(erf) */;
   float eps; float drop_p; unsigned long long seed;

@@ -127,14 +127,43 @@ def test_norm_act_dropout_is_consistent(cuda_device):
     assert x.grad.abs().max().item() == 0.0
 
 
+def test_norm_act_bwd_second_addend_and_colsum(cuda_device):
+    """Backward extras used by the one-node encoder layer: ``dout2`` is added to ``dout`` inside the kernel and
+    ``dcolsum`` = column sums of ``d_in0`` (the bias gradient of the Linear that produced in0)."""
+    from vit_spectre_experiments_b200.fused import na_bwd, na_fwd
+
+    torch.manual_seed(9)
+    for dt, tol in ((torch.float32, 2e-5), (torch.bfloat16, 1e-2)):
+        rows, N = 1000, 384
+        in0 = torch.randn(rows, N, device=cuda_device).to(dt)
+        skip = torch.randn(rows, N, device=cuda_device).to(dt)
+        gamma = 1 + 0.2 * torch.randn(N, device=cuda_device)
+        beta = 0.1 * torch.randn(N, device=cuda_device)
+        da, db = torch.randn(rows, N, device=cuda_device).to(dt), torch.randn(rows, N, device=cuda_device).to(dt)
+        out, mean, rstd = na_fwd(in0, gamma, beta, skip=skip, act=1)
+        d_in0, d_skip, dg, dbt, dcol = na_bwd(da, in0, gamma, beta, mean, rstd, skip_shape=(rows, N), act=1, dout2=db,
+                                              colsum=True)
+        x = in0.float().requires_grad_(True)
+        sk = skip.float().requires_grad_(True)
+        g2, b2 = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+        y = F.gelu(F.layer_norm(x, (N,), g2, b2)) + sk
+        y.backward(da.float() + db.float())
+        assert rel_err(d_in0, x.grad) <= tol and rel_err(d_skip, sk.grad) <= tol
+        assert rel_err(dg, g2.grad) <= 3e-5 and rel_err(dbt, b2.grad) <= 3e-5
+        assert rel_err(dcol, d_in0.float().sum(0)) <= 1e-5
+
+
+@pytest.mark.parametrize("mixer,grid", [("fft", (8, 8)), ("dwt", (8, 8)), ("permut", None)])
 @pytest.mark.parametrize("autocast", [False, True])
-def test_encoder_layer_fused_matches_torch(cuda_device, autocast):
-    """Whole SpectreEncoderLayer: fused path == stock torch composition (same parameters, same input)."""
+def test_encoder_layer_fused_matches_torch(cuda_device, autocast, mixer, grid):
+    """Whole SpectreEncoderLayer: fused path == stock torch composition (same parameters, same input).  With a CUDA
+    mixer in the slot the fused path is the one-node ``fused.encoder_layer``; with MHPermutMix it is the
+    per-kernel autograd composition."""
     from vit_spectre_experiments_b200 import SpectreEncoderLayer
 
     torch.manual_seed(3)
-    kw = dict(seq_length=65, d_model=128, nhead=4, dim_feedforward=256, dropout=0.0, activation="gelu", mixer="fft",
-              grid=(8, 8))
+    kw = dict(seq_length=65, d_model=128, nhead=4, dim_feedforward=256, dropout=0.0, activation="gelu", mixer=mixer,
+              grid=grid)
     a = SpectreEncoderLayer(**kw, fused=True).to(cuda_device)
     b = SpectreEncoderLayer(**kw, fused=False).to(cuda_device)
     b.load_state_dict(a.state_dict())

@@ -35,8 +35,8 @@ class NormActDesc(ctypes.Structure):
     _fields_ = [
         ("in0", ctypes.c_void_p), ("in1", ctypes.c_void_p), ("gamma", ctypes.c_void_p), ("beta", ctypes.c_void_p),
         ("skip", ctypes.c_void_p), ("out", ctypes.c_void_p), ("mean", ctypes.c_void_p), ("rstd", ctypes.c_void_p),
-        ("dout", ctypes.c_void_p), ("d_in0", ctypes.c_void_p), ("d_skip", ctypes.c_void_p),
-        ("dgamma", ctypes.c_void_p), ("dbeta", ctypes.c_void_p), ("workspace", ctypes.c_void_p),
+        ("dout", ctypes.c_void_p), ("dout2", ctypes.c_void_p), ("d_in0", ctypes.c_void_p), ("d_skip", ctypes.c_void_p),
+        ("dgamma", ctypes.c_void_p), ("dbeta", ctypes.c_void_p), ("dcolsum", ctypes.c_void_p), ("workspace", ctypes.c_void_p),
         ("workspace_bytes", ctypes.c_size_t), ("rows", ctypes.c_longlong), ("N", ctypes.c_int), ("Ns", ctypes.c_int),
         ("act_dtype", ctypes.c_int), ("act", ctypes.c_int), ("eps", ctypes.c_float), ("drop_p", ctypes.c_float),
         ("seed", ctypes.c_ulonglong),

@@ -5,6 +5,7 @@ __base__ = "default.py"
 mixer = "fft"
 precision = "bf16"
 batch_size = 256
+bench_batch_size = 1024         # per-GPU batch of bench.py: sized for 180 GB HBM3e (B=256 leaves each mixer launch at ~12 us of HBM time)
 val_batch_size = 256
 epochs = 300
 num_classes = 1000

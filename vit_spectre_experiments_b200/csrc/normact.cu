@@ -43,8 +43,9 @@ constexpr int down_k(int mode) { return mode == kSkipDown2 ? 2 : mode == kSkipDo
 struct Args {
   const void* in0; const void* in1; const float* gamma; const float* beta; const void* skip;
   void* out; float* mean; float* rstd;
-  const void* dout;
-  void* d_in0; void* d_skip; float* part;   // part: [grid][2][N] gamma/beta partials
+  const void* dout; const void* dout2;   // upstream gradient (+ optional second addend)
+  void* d_in0; void* d_skip; float* part;   // part: [grid][nacc][N] partials: dgamma, dbeta (, column sums of d_in0)
+  int nacc;
   long long rows; int N; int Ns; int act; int skip_mode;
   int tpr; int rpc;                                                 // threads per row, rows per CTA
   int stages; int stage_bytes;                                      // shared-memory ring of input row groups
@@ -397,11 +398,12 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   const int tpr = a.tpr, wpr = tpr >> 5;
   const int rg = threadIdx.x / tpr, t = threadIdx.x - rg * tpr;
   const int nvec = a.N >> 3, S = a.stages;
-  // per-row-group gamma/beta gradient accumulators [rpc][2][N] (a thread only ever touches its own columns
+  // per-row-group gamma/beta (/ column-sum) accumulators [rpc][nacc][N] (a thread only ever touches its own columns
   // of its own row group: no conflicts, and 32 registers less than keeping them in the register file)
   float* accs = reinterpret_cast<float*>(ring + S * a.stage_bytes);
-  float* sgam = accs + a.rpc * 2 * a.N;                               // [N] gamma, [N] beta
-  float* myacc = accs + rg * 2 * a.N;
+  const int nacc = a.nacc;                                            // 2, or 3 with the column sums of d_in0
+  float* sgam = accs + a.rpc * nacc * a.N;                            // [N] gamma, [N] beta
+  float* myacc = accs + rg * nacc * a.N;
   const float inv_n = 1.0f / static_cast<float>(a.N);
   const bool drop = a.drop_p > 0.f;
   const unsigned thresh = drop ? static_cast<unsigned>(fminf(a.drop_p, 0.999999f) * 4294967296.0f) : 0u;
@@ -409,6 +411,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   const long long groups = (a.rows + a.rpc - 1) / a.rpc;
   const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
   const int off_in0 = a.rpc * a.N * static_cast<int>(sizeof(T)), off_in1 = 2 * off_in0;
+  const int off_d2 = off_in0 * (a.in1 ? 3 : 2);
 
   auto issue = [&](int it, int stg) {   // dout, in0 (, in1) of one row group: contiguous, one bulk copy each
     const long long row0 = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc;
@@ -417,10 +420,11 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
     uint8_t* st = ring + stg * a.stage_bytes;
     uint64_t* bar = &full[stg];
     const uint32_t bmain = nr * a.N * sizeof(T);
-    ptx::mbar_arrive_expect_tx(bar, bmain * (a.in1 ? 3u : 2u));
+    ptx::mbar_arrive_expect_tx(bar, bmain * (2u + (a.in1 ? 1u : 0u) + (a.dout2 ? 1u : 0u)));
     bulk_load(st, static_cast<const T*>(a.dout) + row0 * a.N, bmain, bar);
     bulk_load(st + off_in0, static_cast<const T*>(a.in0) + row0 * a.N, bmain, bar);
     if (a.in1) bulk_load(st + off_in1, static_cast<const T*>(a.in1) + row0 * a.N, bmain, bar);
+    if (a.dout2) bulk_load(st + off_d2, static_cast<const T*>(a.dout2) + row0 * a.N, bmain, bar);
   };
   if (threadIdx.x == 0) {
     for (int k = 0; k < S; ++k) ptx::mbar_init(&full[k], 1);
@@ -431,7 +435,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
     sgam[i] = a.gamma[i];
     sgam[a.N + i] = a.beta[i];
   }
-  for (int i = threadIdx.x; i < a.rpc * 2 * a.N; i += blockDim.x) accs[i] = 0.f;
+  for (int i = threadIdx.x; i < a.rpc * nacc * a.N; i += blockDim.x) accs[i] = 0.f;
   __syncthreads();
 
   // row statistics of the first row (prefetched one iteration ahead afterwards)
@@ -474,6 +478,12 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
         ld8(reinterpret_cast<const T*>(st + off_in1) + rg * a.N + j0, w);
 #pragma unroll
         for (int e = 0; e < 8; ++e) z[e] += w[e];
+      }
+      if (a.dout2) {
+        float w[8];
+        ld8(reinterpret_cast<const T*>(st + off_d2) + rg * a.N + j0, w);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) d[e] += w[e];
       }
       if (drop) {
         const unsigned vh = vec_hash(rseed, static_cast<unsigned>(v));
@@ -523,6 +533,13 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) dz[e] = rstd * (gy[i][e] - m1 - xh[i][e] * m2);
         st8(static_cast<T*>(a.d_in0) + row * a.N + v * 8, dz);
+        if (nacc == 3) {   // column sums of d_in0: the bias gradient of the Linear that produced in0
+          float cs[8];
+          ld8(myacc + 2 * a.N + v * 8, cs);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) cs[e] += dz[e];
+          st8(myacc + 2 * a.N + v * 8, cs);
+        }
       }
     }
     __syncthreads();   // stage consumed
@@ -530,10 +547,10 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   }
   // fold the row groups of the CTA in a fixed order: one partial [2][N] per CTA  (the loop's last barrier
   // already ordered every accumulator update)
-  float* pg = a.part + static_cast<size_t>(blockIdx.x) * 2 * a.N;
-  for (int c = threadIdx.x; c < 2 * a.N; c += blockDim.x) {
+  float* pg = a.part + static_cast<size_t>(blockIdx.x) * nacc * a.N;
+  for (int c = threadIdx.x; c < nacc * a.N; c += blockDim.x) {
     float v = accs[c];
-    for (int r = 1; r < a.rpc; ++r) v += accs[r * 2 * a.N + c];
+    for (int r = 1; r < a.rpc; ++r) v += accs[r * nacc * a.N + c];
     pg[c] = v;
   }
 }
@@ -557,20 +574,23 @@ __global__ void pool_bwd_general_kernel(const Args a) {
     const int e = static_cast<int>((static_cast<long long>(j + 1) * a.Ns + a.N - 1) / a.N);
     if (c < s || c >= e) continue;
     float d = ld1(static_cast<const T*>(a.dout) + row * a.N + j);
+    if (a.dout2) d += ld1(static_cast<const T*>(a.dout2) + row * a.N + j);
     if (drop) d = keep(rseed, static_cast<unsigned>(j), thresh) ? d * keep_scale : 0.f;
     acc += d / static_cast<float>(e - s);
   }
   st1(static_cast<T*>(a.d_skip) + i, acc);
 }
 
-// dgamma[c] = sum_s part[s][0][c], dbeta[c] = sum_s part[s][1][c].  CTA = 32 columns x 8 slab lanes; the
+// out_k[c] = sum_s part[s][k][c] for k < nacc (dgamma, dbeta, column sums).  CTA = 32 columns x 8 slab lanes; the
 // eight lane sums are combined in a fixed order (deterministic).
 __global__ void __launch_bounds__(256) reduce_gamma_beta_kernel(const float* __restrict__ part, float* __restrict__ dgamma,
-                                                                float* __restrict__ dbeta, int N, int slabs) {
+                                                                float* __restrict__ dbeta, float* __restrict__ dsum, int N,
+                                                                int nacc, int slabs) {
   __shared__ float sm[8][33];
   const int col = blockIdx.x * 32 + (threadIdx.x & 31), ln = threadIdx.x >> 5;
+  const int ncol = nacc * N;
   float s0 = 0.f, s1 = 0.f;
-  if (col < 2 * N) {
+  if (col < ncol) {
     // 8 independent loads in flight per thread; partial sums are combined in a fixed order
     float acc[8];
 #pragma unroll
@@ -578,20 +598,21 @@ __global__ void __launch_bounds__(256) reduce_gamma_beta_kernel(const float* __r
     int k = ln;
     for (; k + 56 < slabs; k += 64) {
 #pragma unroll
-      for (int u = 0; u < 8; ++u) acc[u] += part[static_cast<size_t>(k + 8 * u) * 2 * N + col];
+      for (int u = 0; u < 8; ++u) acc[u] += part[static_cast<size_t>(k + 8 * u) * ncol + col];
     }
-    for (; k < slabs; k += 8) acc[0] += part[static_cast<size_t>(k) * 2 * N + col];
+    for (; k < slabs; k += 8) acc[0] += part[static_cast<size_t>(k) * ncol + col];
     s0 = ((acc[0] + acc[1]) + (acc[2] + acc[3]));
     s1 = ((acc[4] + acc[5]) + (acc[6] + acc[7]));
   }
   sm[ln][threadIdx.x & 31] = s0 + s1;
   __syncthreads();
-  if (ln == 0 && col < 2 * N) {
+  if (ln == 0 && col < ncol) {
     float s = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) s += sm[k][threadIdx.x];
     if (col < N) dgamma[col] = s;
-    else dbeta[col - N] = s;
+    else if (col < 2 * N) dbeta[col - N] = s;
+    else dsum[col - 2 * N] = s;
   }
 }
 
@@ -614,13 +635,15 @@ struct Shape {
   int vpt, tpr, rpc, stages, stage_bytes;
   size_t smem;   // dynamic shared memory of the launch
 };
-static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, bool bwd) {
+static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, bool bwd, bool has_dout2 = false,
+                          int nacc = 2) {
   Shape sh{};
   const int nvec = N / 8;
   if (nvec <= 32) { sh.vpt = 1; sh.tpr = 32; }
   else { sh.vpt = 2; sh.tpr = ((nvec + 1) / 2 + 31) / 32 * 32; }
   // bytes of one row in the ring: forward in0 (+ in1) + skip; backward dout + in0 (+ in1)
-  const int row_bytes = bwd ? N * elem * (has_in1 ? 3 : 2) : N * elem * (has_in1 ? 2 : 1) + (has_skip ? Ns * elem : 0);
+  const int row_bytes = bwd ? N * elem * (2 + (has_in1 ? 1 : 0) + (has_dout2 ? 1 : 0))
+                            : N * elem * (has_in1 ? 2 : 1) + (has_skip ? Ns * elem : 0);
   sh.rpc = 256 / sh.tpr;
   while (sh.rpc > 1 && sh.rpc * row_bytes > 48 * 1024) sh.rpc /= 2;
   if (sh.rpc < 1) sh.rpc = 1;
@@ -628,7 +651,7 @@ static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, 
   sh.stages = (bwd ? 36 : 64) * 1024 / sh.stage_bytes;
   if (sh.stages < 2) sh.stages = 2;
   if (sh.stages > kMaxStages) sh.stages = kMaxStages;
-  sh.smem = static_cast<size_t>(sh.stages) * sh.stage_bytes + (bwd ? static_cast<size_t>(2 * sh.rpc + 2) * N * sizeof(float) : 0);
+  sh.smem = static_cast<size_t>(sh.stages) * sh.stage_bytes + (bwd ? static_cast<size_t>(nacc * sh.rpc + 2) * N * sizeof(float) : 0);
   return sh;
 }
 
@@ -643,8 +666,8 @@ static int validate(const char* fn, const spectre_norm_act_t* d, bool bwd) {
   if (d->act_dtype != SPECTRE_DTYPE_F32 && d->act_dtype != SPECTRE_DTYPE_BF16)
     return fail(SPECTRE_E_DTYPE, "%s: act_dtype=%d (0=float32, 1=bfloat16)", fn, d->act_dtype);
   if (d->drop_p < 0.f || d->drop_p >= 1.f) return fail(SPECTRE_E_SHAPE, "%s: drop_p=%g outside [0,1)", fn, d->drop_p);
-  const void* ptrs[] = {d->in0, d->in1, d->gamma, d->beta, d->skip, d->out, d->dout,
-                        d->d_in0, d->d_skip, d->dgamma, d->dbeta, d->workspace};
+  const void* ptrs[] = {d->in0, d->in1, d->gamma, d->beta, d->skip, d->out, d->dout, d->dout2,
+                        d->d_in0, d->d_skip, d->dgamma, d->dbeta, d->dcolsum, d->workspace};
   for (const void* q : ptrs)
     if (!aligned16(q)) return fail(SPECTRE_E_ALIGN, "%s: pointers must be 16-byte aligned", fn);
   if (!bwd && !d->out) return fail(SPECTRE_E_NULL, "%s: null out", fn);
@@ -656,7 +679,8 @@ static Args to_args(const spectre_norm_act_t& d, bool bwd) {
   Args a{};
   a.in0 = d.in0; a.in1 = d.in1; a.gamma = d.gamma; a.beta = d.beta; a.skip = d.skip;
   a.out = d.out; a.mean = d.mean; a.rstd = d.rstd;
-  a.dout = d.dout; a.d_in0 = d.d_in0; a.d_skip = d.d_skip;
+  a.dout = d.dout; a.dout2 = bwd ? d.dout2 : nullptr; a.d_in0 = d.d_in0; a.d_skip = d.d_skip;
+  a.nacc = (bwd && d.dcolsum) ? 3 : 2;
   a.part = static_cast<float*>(d.workspace);
   const bool has_skip = bwd ? d.d_skip != nullptr : d.skip != nullptr;
   a.rows = d.rows; a.N = d.N; a.Ns = has_skip ? d.Ns : d.N; a.act = d.act; a.eps = d.eps; a.drop_p = d.drop_p;
@@ -730,16 +754,17 @@ int spectre_norm_act_fwd(const spectre_norm_act_t* d, void* stream) {
   return SPECTRE_OK;
 }
 
-// upper bound over both element types (the query has no dtype argument)
+// upper bound over element types / optional operands (the query has no such arguments)
 size_t spectre_norm_act_bwd_workspace_bytes(long long rows, int N) {
   if (rows < 1 || N < 8) return 0;
   size_t best = 0;
   for (int elem : {2, 4})
-    for (int in1 : {0, 1}) {
-      const Shape sh = launch_shape(N, N, in1 != 0, false, elem, true);
-      const size_t b = static_cast<size_t>(grid_for(rows, sh)) * 2 * N * sizeof(float);
-      if (b > best) best = b;
-    }
+    for (int extra = 0; extra < 3; ++extra)
+      for (int nacc : {2, 3}) {
+        const Shape sh = launch_shape(N, N, extra >= 1, false, elem, true, extra >= 2, nacc);
+        const size_t b = static_cast<size_t>(grid_for(rows, sh)) * 3 * N * sizeof(float);
+        if (b > best) best = b;
+      }
   return best;
 }
 
@@ -747,12 +772,12 @@ int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
   if (int rc = validate("spectre_norm_act_bwd", d, true)) return rc;
   Args a = to_args(*d, true);
   const bool bf = d->act_dtype == SPECTRE_DTYPE_BF16;
-  const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, false, bf ? 2 : 4, true);
+  const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, false, bf ? 2 : 4, true, a.dout2 != nullptr, a.nacc);
   a.tpr = sh.tpr; a.rpc = sh.rpc; a.stages = sh.stages; a.stage_bytes = sh.stage_bytes;
   const int grid = grid_for(a.rows, sh), block = sh.tpr * sh.rpc;
-  if (!d->workspace || d->workspace_bytes < static_cast<size_t>(grid) * 2 * a.N * sizeof(float))
+  if (!d->workspace || d->workspace_bytes < static_cast<size_t>(grid) * a.nacc * a.N * sizeof(float))
     return fail(SPECTRE_E_WORKSPACE, "spectre_norm_act_bwd: workspace %zu B < required %zu B", d->workspace_bytes,
-                static_cast<size_t>(grid) * 2 * a.N * sizeof(float));
+                static_cast<size_t>(grid) * a.nacc * a.N * sizeof(float));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   table().bwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
   int launches = 1;
@@ -762,7 +787,7 @@ int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
     else pool_bwd_general_kernel<float><<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a);
     ++launches;
   }
-  reduce_gamma_beta_kernel<<<(2 * a.N + 31) / 32, 256, 0, st>>>(a.part, d->dgamma, d->dbeta, a.N, grid);
+  reduce_gamma_beta_kernel<<<(a.nacc * a.N + 31) / 32, 256, 0, st>>>(a.part, d->dgamma, d->dbeta, d->dcolsum, a.N, a.nacc, grid);
   ++launches;
   last_launch_count() = launches;
   const cudaError_t err = cudaGetLastError();

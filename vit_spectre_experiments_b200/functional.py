@@ -78,98 +78,83 @@ def _check_tokens(x: torch.Tensor, H: int, W: int, has_cls: bool, what: str) -> 
         )
 
 
-class _FFTMix(torch.autograd.Function):
+# ------------------------------------------------------------------ raw (non-autograd) kernel calls
+def _mix_fwd_raw(kind, x, param, H, W, has_cls):
+    lib = _lib.load()
+    what = f"{kind}_mix"
+    _check_tokens(x, H, W, has_cls, what)
+    code = _act_code(x, what)
+    E = x.shape[2]
+    want = (H, W // 2 + 1, E, 2) if kind == "fft" else (4, H // 2, W // 2, E)
+    if param.dtype != torch.float32 or tuple(param.shape) != want:
+        name = "filter" if kind == "fft" else "weight"
+        raise RuntimeError(f"{what}: {name} must be float32 {list(want)}, got {param.dtype} {tuple(param.shape)}")
+    y = torch.empty_like(x)
+    B = x.shape[0]
+    fn = lib.spectre_fftmix_fwd if kind == "fft" else lib.spectre_dwtmix_fwd
+    with torch.cuda.device(x.device):
+        with _timed(f"{kind}mix_fwd", (B, H, W, E, x.element_size())):
+            rc = fn(x.data_ptr(), param.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls), code, _stream_ptr(x.device))
+    _lib.check(rc, f"spectre_{kind}mix_fwd")
+    _lib.count_launches()
+    return y
+
+
+def _mix_bwd_raw(kind, dy, x, param, H, W, has_cls):
+    lib = _lib.load()
+    B, _, E = x.shape
+    dx = torch.empty_like(x)
+    dparam = torch.empty_like(param)
+    ws_fn = lib.spectre_fftmix_bwd_workspace_bytes if kind == "fft" else lib.spectre_dwtmix_bwd_workspace_bytes
+    fn = lib.spectre_fftmix_bwd if kind == "fft" else lib.spectre_dwtmix_bwd
+    with torch.cuda.device(x.device):
+        nbytes = ws_fn(B, H, W, E)
+        ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
+        with _timed(f"{kind}mix_bwd", (B, H, W, E, x.element_size())):
+            rc = fn(dy.data_ptr(), x.data_ptr(), param.data_ptr(), dx.data_ptr(), dparam.data_ptr(), ws.data_ptr(),
+                    nbytes, B, H, W, E, int(has_cls), _act_code(x, f"{kind}_mix"), _stream_ptr(x.device))
+    _lib.check(rc, f"spectre_{kind}mix_bwd")
+    _lib.count_launches()
+    return dx, dparam
+
+
+def fftmix_fwd_raw(x, filt, H, W, has_cls):
+    """``spectre_fftmix_fwd`` on contiguous ``x [B,T,E]`` (fp32 / bf16) and float32 ``filt``; returns ``y``."""
+    return _mix_fwd_raw("fft", x, filt, H, W, has_cls)
+
+
+def fftmix_bwd_raw(dy, x, filt, H, W, has_cls):
+    """``spectre_fftmix_bwd``: returns ``(dx, dfilt)``."""
+    return _mix_bwd_raw("fft", dy, x, filt, H, W, has_cls)
+
+
+def dwtmix_fwd_raw(x, weight, H, W, has_cls):
+    return _mix_fwd_raw("dwt", x, weight, H, W, has_cls)
+
+
+def dwtmix_bwd_raw(dy, x, weight, H, W, has_cls):
+    return _mix_bwd_raw("dwt", dy, x, weight, H, W, has_cls)
+
+
+class _Mix(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, filt, H, W, has_cls):
-        lib = _lib.load()
-        _check_tokens(x, H, W, has_cls, "fft_mix")
-        code = _act_code(x, "fft_mix")
-        if filt.dtype != torch.float32 or tuple(filt.shape) != (H, W // 2 + 1, x.shape[2], 2):
-            raise RuntimeError(
-                f"fft_mix: filter must be float32 [{H}, {W // 2 + 1}, {x.shape[2]}, 2], got {filt.dtype} {tuple(filt.shape)}"
-            )
+    def forward(ctx, x, param, kind, H, W, has_cls):
         x = x.contiguous()
-        filt = filt.contiguous()
-        y = torch.empty_like(x)
-        B, _, E = x.shape
-        with torch.cuda.device(x.device):
-            with _timed("fftmix_fwd", (B, H, W, E, x.element_size())):
-                rc = lib.spectre_fftmix_fwd(x.data_ptr(), filt.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls),
-                                            code, _stream_ptr(x.device))
-        _lib.check(rc, "spectre_fftmix_fwd")
-        _lib.count_launches()
-        ctx.save_for_backward(x, filt)
-        ctx.grid = (H, W, has_cls)
+        param = param.contiguous()
+        y = _mix_fwd_raw(kind, x, param, H, W, has_cls)
+        ctx.save_for_backward(x, param)
+        ctx.cfg = (kind, H, W, has_cls)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        lib = _lib.load()
-        x, filt = ctx.saved_tensors
-        H, W, has_cls = ctx.grid
-        B, _, E = x.shape
+        x, param = ctx.saved_tensors
+        kind, H, W, has_cls = ctx.cfg
         dy = dy.contiguous()
         if dy.dtype != x.dtype:
             dy = dy.to(x.dtype)
-        dx = torch.empty_like(x)
-        dfilt = torch.empty_like(filt)
-        with torch.cuda.device(x.device):
-            nbytes = lib.spectre_fftmix_bwd_workspace_bytes(B, H, W, E)
-            ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
-            with _timed("fftmix_bwd", (B, H, W, E, x.element_size())):
-                rc = lib.spectre_fftmix_bwd(dy.data_ptr(), x.data_ptr(), filt.data_ptr(), dx.data_ptr(),
-                                            dfilt.data_ptr(), ws.data_ptr(), nbytes, B, H, W, E, int(has_cls),
-                                            _act_code(x, "fft_mix"), _stream_ptr(x.device))
-        _lib.check(rc, "spectre_fftmix_bwd")
-        _lib.count_launches()
-        return dx, dfilt, None, None, None
-
-
-class _DWTMix(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, x, weight, H, W, has_cls):
-        lib = _lib.load()
-        _check_tokens(x, H, W, has_cls, "dwt_mix")
-        code = _act_code(x, "dwt_mix")
-        if weight.dtype != torch.float32 or tuple(weight.shape) != (4, H // 2, W // 2, x.shape[2]):
-            raise RuntimeError(
-                f"dwt_mix: weight must be float32 [4, {H // 2}, {W // 2}, {x.shape[2]}], got {weight.dtype} {tuple(weight.shape)}"
-            )
-        x = x.contiguous()
-        weight = weight.contiguous()
-        y = torch.empty_like(x)
-        B, _, E = x.shape
-        with torch.cuda.device(x.device):
-            with _timed("dwtmix_fwd", (B, H, W, E, x.element_size())):
-                rc = lib.spectre_dwtmix_fwd(x.data_ptr(), weight.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls),
-                                            code, _stream_ptr(x.device))
-        _lib.check(rc, "spectre_dwtmix_fwd")
-        _lib.count_launches()
-        ctx.save_for_backward(x, weight)
-        ctx.grid = (H, W, has_cls)
-        return y
-
-    @staticmethod
-    def backward(ctx, dy):
-        lib = _lib.load()
-        x, weight = ctx.saved_tensors
-        H, W, has_cls = ctx.grid
-        B, _, E = x.shape
-        dy = dy.contiguous()
-        if dy.dtype != x.dtype:
-            dy = dy.to(x.dtype)
-        dx = torch.empty_like(x)
-        dw = torch.empty_like(weight)
-        with torch.cuda.device(x.device):
-            nbytes = lib.spectre_dwtmix_bwd_workspace_bytes(B, H, W, E)
-            ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
-            with _timed("dwtmix_bwd", (B, H, W, E, x.element_size())):
-                rc = lib.spectre_dwtmix_bwd(dy.data_ptr(), x.data_ptr(), weight.data_ptr(), dx.data_ptr(),
-                                            dw.data_ptr(), ws.data_ptr(), nbytes, B, H, W, E, int(has_cls),
-                                            _act_code(x, "dwt_mix"), _stream_ptr(x.device))
-        _lib.check(rc, "spectre_dwtmix_bwd")
-        _lib.count_launches()
-        return dx, dw, None, None, None
+        dx, dparam = _mix_bwd_raw(kind, dy, x, param, H, W, has_cls)
+        return dx, dparam, None, None, None, None
 
 
 def fft_mix(x: torch.Tensor, filt: torch.Tensor, grid, has_cls: bool = True) -> torch.Tensor:
@@ -178,7 +163,7 @@ def fft_mix(x: torch.Tensor, filt: torch.Tensor, grid, has_cls: bool = True) -> 
     x ``[B, has_cls + H*W, E]`` (float32 or bfloat16, CUDA); filt float32 ``[H, W//2+1, E, 2]``.
     """
     H, W = grid
-    return _FFTMix.apply(x, filt, int(H), int(W), bool(has_cls))
+    return _Mix.apply(x, filt, "fft", int(H), int(W), bool(has_cls))
 
 
 def dwt_mix(x: torch.Tensor, weight: torch.Tensor, grid, has_cls: bool = True) -> torch.Tensor:
@@ -187,4 +172,4 @@ def dwt_mix(x: torch.Tensor, weight: torch.Tensor, grid, has_cls: bool = True) -
     weight float32 ``[4, H/2, W/2, E]`` ordered (LL, W-low/H-high, W-high/H-low, HH).
     """
     H, W = grid
-    return _DWTMix.apply(x, weight, int(H), int(W), bool(has_cls))
+    return _Mix.apply(x, weight, "dwt", int(H), int(W), bool(has_cls))

@@ -9,8 +9,16 @@ fp32 LayerNorm outputs; statistics and arithmetic stay fp32).
 
 One CUDA pass each way replaces the LayerNorm / GELU / AdaptiveAvgPool1d / add / dropout launches of
 ``SpectreEncoderLayer.forward`` (``spectre_vit/models/spectre/spectre.py:65-73``) and
-``SpectreLinear.forward`` (``spectre_vit/models/spectre/layers.py:95-101``).  CUDA only, no fallback:
-the torch composition of the same modules stays the (CPU-capable) reference path in ``model.py``.
+``SpectreLinear.forward`` (``spectre_vit/models/spectre/layers.py:95-101``).  Two levels:
+
+* :func:`norm_act` -- one tail as an autograd function;
+* :func:`encoder_layer` -- the whole layer (mixer, four tails, two GEMMs) as ONE autograd node with a
+  hand-scheduled backward: gradient sums are folded into kernels that run anyway (second ``dout``
+  operand of the tail backward, ``addmm`` epilogue of the input-gradient GEMMs) and the Linear bias
+  gradients come out of the tail backward as column sums, so no stand-alone add / reduce launches remain.
+
+CUDA only, no fallback: the torch composition of the same modules stays the (CPU-capable) reference path
+in ``model.py``.
 """
 from __future__ import annotations
 
@@ -19,7 +27,7 @@ import ctypes
 import torch
 
 from . import _lib
-from .functional import TIMER, _stream_ptr, _timed
+from .functional import _stream_ptr, _timed, dwtmix_bwd_raw, dwtmix_fwd_raw, fftmix_bwd_raw, fftmix_fwd_raw
 
 _DT = {torch.float32: 0, torch.bfloat16: 1}
 
@@ -28,65 +36,83 @@ def _ptr(t):
     return None if t is None else t.data_ptr()
 
 
+# ------------------------------------------------------------------ raw (non-autograd) kernel calls
+def na_fwd(in0, gamma, beta, in1=None, skip=None, eps=1e-5, act=0, drop_p=0.0, seed=0):
+    """One forward tail.  Returns ``(out, mean, rstd)``; operands must already share in0's dtype."""
+    lib = _lib.load()
+    if not in0.is_cuda:
+        raise RuntimeError("norm_act: CUDA (sm_100a) only; there is no CPU fallback")
+    if in0.dtype not in _DT:
+        raise RuntimeError(f"norm_act: in0 must be float32 or bfloat16, got {in0.dtype}")
+    N = in0.shape[-1]
+    rows = in0.numel() // N
+    out = torch.empty_like(in0)
+    mean = torch.empty(rows, dtype=torch.float32, device=in0.device)
+    rstd = torch.empty_like(mean)
+    d = _lib.NormActDesc()
+    d.in0, d.in1, d.gamma, d.beta, d.skip = _ptr(in0), _ptr(in1), _ptr(gamma), _ptr(beta), _ptr(skip)
+    d.out, d.mean, d.rstd = _ptr(out), _ptr(mean), _ptr(rstd)
+    d.rows, d.N, d.Ns = rows, N, (skip.shape[-1] if skip is not None else N)
+    d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
+    with torch.cuda.device(in0.device):
+        with _timed("norm_act_fwd", (rows, N, in0.element_size())):
+            rc = lib.spectre_norm_act_fwd(ctypes.byref(d), _stream_ptr(in0.device))
+    _lib.check(rc, "spectre_norm_act_fwd")
+    _lib.count_launches()
+    return out, mean, rstd
+
+
+def na_bwd(dout, in0, gamma, beta, mean, rstd, in1=None, skip_shape=None, eps=1e-5, act=0, drop_p=0.0, seed=0,
+           dout2=None, colsum=False):
+    """One backward tail.  Returns ``(d_in0, d_skip | None, dgamma, dbeta, dcolsum | None)``; ``d_in0`` is also
+    the gradient of ``in1``; ``dcolsum`` = column sums of ``d_in0`` (fp32)."""
+    lib = _lib.load()
+    N = in0.shape[-1]
+    rows = in0.numel() // N
+    dev = in0.device
+    d_in0 = torch.empty_like(in0)
+    d_skip = torch.empty(skip_shape, dtype=in0.dtype, device=dev) if skip_shape is not None else None
+    dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(beta)
+    dcol = torch.empty_like(gamma) if colsum else None
+    d = _lib.NormActDesc()
+    d.in0, d.in1, d.gamma, d.beta = _ptr(in0), _ptr(in1), _ptr(gamma), _ptr(beta)
+    d.mean, d.rstd, d.dout, d.dout2 = _ptr(mean), _ptr(rstd), _ptr(dout), _ptr(dout2)
+    d.d_in0, d.d_skip, d.dgamma, d.dbeta, d.dcolsum = _ptr(d_in0), _ptr(d_skip), _ptr(dgamma), _ptr(dbeta), _ptr(dcol)
+    d.rows, d.N, d.Ns = rows, N, (skip_shape[-1] if skip_shape is not None else N)
+    d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
+    with torch.cuda.device(dev):
+        nws = lib.spectre_norm_act_bwd_workspace_bytes(rows, N)
+        ws = torch.empty(max(nws, 16), dtype=torch.uint8, device=dev)
+        d.workspace, d.workspace_bytes = ws.data_ptr(), nws
+        with _timed("norm_act_bwd", (rows, N, in0.element_size())):
+            rc = lib.spectre_norm_act_bwd(ctypes.byref(d), _stream_ptr(dev))
+    _lib.check(rc, "spectre_norm_act_bwd")
+    _lib.count_launches()
+    return d_in0, d_skip, dgamma, dbeta, dcol
+
+
+# ------------------------------------------------------------------ one tail as an autograd function
 class _NormAct(torch.autograd.Function):
     """All activation operands share ``in0``'s dtype (float32, or bfloat16 for the bf16 stream)."""
 
     @staticmethod
     def forward(ctx, in0, in1, skip, gamma, beta, eps, act, drop_p, seed):
-        lib = _lib.load()
-        if not in0.is_cuda:
-            raise RuntimeError("norm_act: CUDA (sm_100a) only; there is no CPU fallback")
-        if in0.dtype not in _DT:
-            raise RuntimeError(f"norm_act: in0 must be float32 or bfloat16, got {in0.dtype}")
-        N = in0.shape[-1]
         in0 = in0.contiguous()
-        rows = in0.numel() // N
         in1 = None if in1 is None else in1.to(in0.dtype).contiguous()
         skip = None if skip is None else skip.to(in0.dtype).contiguous()
         gamma, beta = gamma.float().contiguous(), beta.float().contiguous()
-        out = torch.empty_like(in0)
-        mean = torch.empty(rows, dtype=torch.float32, device=in0.device)
-        rstd = torch.empty_like(mean)
-        d = _lib.NormActDesc()
-        d.in0, d.in1, d.gamma, d.beta, d.skip = _ptr(in0), _ptr(in1), _ptr(gamma), _ptr(beta), _ptr(skip)
-        d.out, d.mean, d.rstd = _ptr(out), _ptr(mean), _ptr(rstd)
-        d.rows, d.N, d.Ns = rows, N, (skip.shape[-1] if skip is not None else N)
-        d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
-        with torch.cuda.device(in0.device):
-            with _timed("norm_act_fwd", (rows, N, in0.element_size())):
-                rc = lib.spectre_norm_act_fwd(ctypes.byref(d), _stream_ptr(in0.device))
-        _lib.check(rc, "spectre_norm_act_fwd")
-        _lib.count_launches()
+        out, mean, rstd = na_fwd(in0, gamma, beta, in1, skip, eps, act, drop_p, seed)
         ctx.save_for_backward(in0, in1, gamma, beta, mean, rstd)
         ctx.meta = (skip.shape if skip is not None else None, float(eps), int(act), float(drop_p), int(seed))
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        lib = _lib.load()
         in0, in1, gamma, beta, mean, rstd = ctx.saved_tensors
         skip_shape, eps, act, drop_p, seed = ctx.meta
-        N = in0.shape[-1]
-        rows = in0.numel() // N
-        dev = in0.device
         dout = dout.to(in0.dtype).contiguous()
-        d_in0 = torch.empty_like(in0)
-        d_skip = torch.empty(skip_shape, dtype=in0.dtype, device=dev) if skip_shape is not None else None
-        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(beta)
-        d = _lib.NormActDesc()
-        d.in0, d.in1, d.gamma, d.beta = _ptr(in0), _ptr(in1), _ptr(gamma), _ptr(beta)
-        d.mean, d.rstd, d.dout = _ptr(mean), _ptr(rstd), _ptr(dout)
-        d.d_in0, d.d_skip, d.dgamma, d.dbeta = _ptr(d_in0), _ptr(d_skip), _ptr(dgamma), _ptr(dbeta)
-        d.rows, d.N, d.Ns = rows, N, (skip_shape[-1] if skip_shape is not None else N)
-        d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], act, eps, drop_p, seed
-        with torch.cuda.device(dev):
-            nws = lib.spectre_norm_act_bwd_workspace_bytes(rows, N)
-            ws = torch.empty(max(nws, 16), dtype=torch.uint8, device=dev)
-            d.workspace, d.workspace_bytes = ws.data_ptr(), nws
-            with _timed("norm_act_bwd", (rows, N, in0.element_size())):
-                rc = lib.spectre_norm_act_bwd(ctypes.byref(d), _stream_ptr(dev))
-        _lib.check(rc, "spectre_norm_act_bwd")
-        _lib.count_launches()
+        d_in0, d_skip, dgamma, dbeta, _ = na_bwd(dout, in0, gamma, beta, mean, rstd, in1, skip_shape, eps, act,
+                                                 drop_p, seed)
         # d(in0 + in1): the same values for both addends
         return d_in0, (d_in0 if in1 is not None else None), d_skip, dgamma, dbeta, None, None, None, None
 
@@ -98,3 +124,75 @@ def norm_act(in0, gamma, beta, *, in1=None, skip=None, eps=1e-5, act="none", dro
     differ).  Returns ``out`` in in0's dtype; statistics and arithmetic are float32.
     """
     return _NormAct.apply(in0, in1, skip, gamma, beta, eps, 1 if act == "gelu" else 0, drop_p, seed)
+
+
+# ------------------------------------------------------------------ the whole encoder layer as one node
+class _EncoderLayer(torch.autograd.Function):
+    """``x1 = LN1(mix(x)) + x ; x2 = LN2(x1 + SL3(drop(SL1(x1))))`` with ``SL(u) = GELU(LN(Linear(u))) + pool(u)``
+    (spectre.py:65-73, layers.py:95-101).  Seven kernels + two GEMMs forward; backward is scheduled by hand."""
+
+    @staticmethod
+    def forward(ctx, x, mix_param, n1w, n1b, w1, b1, l1w, l1b, w3, b3, l3w, l3b, n2w, n2b, cfg):
+        kind, H, W, has_cls, eps, p1, p2, seed1, seed2 = cfg
+        x = x.contiguous()
+        dt = x.dtype
+        B, T, E = x.shape
+        rows = B * T
+        f32 = lambda t: t.detach().float().contiguous()   # noqa: E731
+        n1w, n1b, l1w, l1b, l3w, l3b, n2w, n2b = map(f32, (n1w, n1b, l1w, l1b, l3w, l3b, n2w, n2b))
+        mp = f32(mix_param)
+        w1c, w3c = w1.detach().to(dt), w3.detach().to(dt)          # GEMM operands in the stream dtype
+        b1c, b3c = b1.detach().to(dt), b3.detach().to(dt)
+        m = (fftmix_fwd_raw if kind == "fft" else dwtmix_fwd_raw)(x, mp, H, W, has_cls)
+        x2d, m2d = x.view(rows, E), m.view(rows, E)
+        x1, mean1, rstd1 = na_fwd(m2d, n1w, n1b, skip=x2d, eps=eps[0])
+        h1 = torch.addmm(b1c, x1, w1c.t())
+        a1, mean2, rstd2 = na_fwd(h1, l1w, l1b, skip=x1, eps=eps[1], act=1, drop_p=p1, seed=seed1)
+        h2 = torch.addmm(b3c, a1, w3c.t())
+        ff, mean3, rstd3 = na_fwd(h2, l3w, l3b, skip=a1, eps=eps[2], act=1, drop_p=p2, seed=seed2)
+        x2, mean4, rstd4 = na_fwd(x1, n2w, n2b, in1=ff, eps=eps[3])
+        ctx.save_for_backward(x, mp, m, x1, h1, a1, h2, ff, w1c, w3c, n1w, n1b, l1w, l1b, l3w, l3b, n2w, n2b,
+                              mean1, rstd1, mean2, rstd2, mean3, rstd3, mean4, rstd4)
+        ctx.cfg = cfg
+        ctx.param_dtypes = (w1.dtype, b1.dtype, w3.dtype, b3.dtype)
+        return x2.view(B, T, E)
+
+    @staticmethod
+    def backward(ctx, d_x2):
+        (x, mp, m, x1, h1, a1, h2, ff, w1c, w3c, n1w, n1b, l1w, l1b, l3w, l3b, n2w, n2b,
+         mean1, rstd1, mean2, rstd2, mean3, rstd3, mean4, rstd4) = ctx.saved_tensors
+        kind, H, W, has_cls, eps, p1, p2, seed1, seed2 = ctx.cfg
+        B, T, E = x.shape
+        rows = B * T
+        hid = h1.shape[-1]
+        d_x2 = d_x2.to(x.dtype).contiguous().view(rows, E)
+        # x2 = LN2(x1 + ff): one gradient for both addends
+        d_z, _, dn2w, dn2b, _ = na_bwd(d_x2, x1, n2w, n2b, mean4, rstd4, in1=ff, eps=eps[3])
+        # ff = GELU(LN(h2)) + pool_down(a1)
+        d_h2, d_a1, dl3w, dl3b, db3 = na_bwd(d_z, h2, l3w, l3b, mean3, rstd3, skip_shape=(rows, hid), eps=eps[2], act=1,
+                                             drop_p=p2, seed=seed2, colsum=True)
+        dw3 = torch.mm(d_h2.t(), a1)
+        d_a1 = torch.addmm(d_a1, d_h2, w3c)                        # skip path + GEMM path in the GEMM epilogue
+        # a1 = drop(GELU(LN(h1)) + pool_up(x1))
+        d_h1, d_x1, dl1w, dl1b, db1 = na_bwd(d_a1, h1, l1w, l1b, mean2, rstd2, skip_shape=(rows, E), eps=eps[1], act=1,
+                                             drop_p=p1, seed=seed1, colsum=True)
+        dw1 = torch.mm(d_h1.t(), x1)
+        d_x1 = torch.addmm(d_x1, d_h1, w1c)
+        # x1 = LN1(m) + x: upstream = d_x1 (skip + GEMM paths) + d_z (LN2 path), summed inside the kernel;
+        # the identity skip hands the summed gradient on as d_x
+        d_m, d_x, dn1w, dn1b, _ = na_bwd(d_x1, m.view(rows, E), n1w, n1b, mean1, rstd1, skip_shape=(rows, E), eps=eps[0],
+                                         dout2=d_z)
+        d_xm, d_mp = (fftmix_bwd_raw if kind == "fft" else dwtmix_bwd_raw)(d_m.view(B, T, E), x, mp, H, W, has_cls)
+        d_x = d_x.view(B, T, E).add_(d_xm)
+        wd1, bd1, wd3, bd3 = ctx.param_dtypes
+        return (d_x, d_mp, dn1w, dn1b, dw1.to(wd1), db1.to(bd1), dl1w, dl1b, dw3.to(wd3), db3.to(bd3), dl3w, dl3b,
+                dn2w, dn2b, None)
+
+
+def encoder_layer(x, mix_kind, mix_param, grid, has_cls, norm1, lin1, ln1, lin3, ln3, norm2, p1, p2, seed1, seed2):
+    """Whole ``SpectreEncoderLayer`` through the fused kernels as one autograd node.  ``x`` is ``[B, T, E]`` in the
+    stream dtype (float32 or bfloat16); modules are the layer's ``nn.LayerNorm`` / ``nn.Linear`` instances."""
+    cfg = (mix_kind, int(grid[0]), int(grid[1]), bool(has_cls), (norm1.eps, ln1.eps, ln3.eps, norm2.eps),
+           float(p1), float(p2), int(seed1), int(seed2))
+    return _EncoderLayer.apply(x, mix_param, norm1.weight, norm1.bias, lin1.weight, lin1.bias, ln1.weight, ln1.bias,
+                               lin3.weight, lin3.bias, ln3.weight, ln3.bias, norm2.weight, norm2.bias, cfg)

@@ -132,23 +132,32 @@ class SpectreEncoderLayer(nn.Module):
     def forward_fused(self, x: torch.Tensor) -> torch.Tensor:
         """Same arithmetic through the fused kernels.  Under bf16 autocast the residual stream is bf16 from
         end to end (one cast at the encoder entry; every kernel reads and writes bf16, statistics fp32);
-        otherwise everything stays float32.  Returns the layer output in the stream dtype."""
-        from .fused import norm_act
+        otherwise everything stays float32.  Returns the layer output in the stream dtype.
+
+        With one of the CUDA mixers in the slot the whole layer is ONE autograd node (``fused.encoder_layer``:
+        hand-scheduled backward, gradient sums and bias gradients folded into the kernels); any other
+        occupant of the slot (``MHPermutMix``, a user module) keeps the per-kernel autograd composition."""
+        from .fused import encoder_layer, norm_act
 
         if torch.is_autocast_enabled() and x.dtype != torch.bfloat16:
             x = x.to(torch.bfloat16)
-        m = self.mix_layer(x)
-        x1 = norm_act(m, self.norm1.weight, self.norm1.bias, skip=x, eps=self.norm1.eps)
         lin1, ln1 = self.linear1.local_head[0], self.linear1.local_head[1]
         lin3, ln3 = self.linear3.local_head[0], self.linear3.local_head[1]
         p1 = self.dropout1.p if self.training else 0.0
         p2 = self.dropout2.p if self.training else 0.0
+        s1 = _dropout_seed() if p1 > 0 else 0
+        s2 = _dropout_seed() if p2 > 0 else 0
+        mix = self.mix_layer
+        if isinstance(mix, (SpectralFilterMix, HaarDWTMix)) and x.dim() == 3:
+            kind, param = ("fft", mix.filter) if isinstance(mix, SpectralFilterMix) else ("dwt", mix.weight)
+            return encoder_layer(x, kind, param, mix.grid, mix.has_cls, self.norm1, lin1, ln1, lin3, ln3, self.norm2,
+                                 p1, p2, s1, s2)
+        m = mix(x)
+        x1 = norm_act(m, self.norm1.weight, self.norm1.bias, skip=x, eps=self.norm1.eps)
         h1 = F.linear(x1, lin1.weight, lin1.bias)
-        a1 = norm_act(h1, ln1.weight, ln1.bias, skip=x1, eps=ln1.eps, act="gelu", drop_p=p1,
-                      seed=_dropout_seed() if p1 > 0 else 0)
+        a1 = norm_act(h1, ln1.weight, ln1.bias, skip=x1, eps=ln1.eps, act="gelu", drop_p=p1, seed=s1)
         h2 = F.linear(a1, lin3.weight, lin3.bias)
-        ff = norm_act(h2, ln3.weight, ln3.bias, skip=a1, eps=ln3.eps, act="gelu", drop_p=p2,
-                      seed=_dropout_seed() if p2 > 0 else 0)
+        ff = norm_act(h2, ln3.weight, ln3.bias, skip=a1, eps=ln3.eps, act="gelu", drop_p=p2, seed=s2)
         return norm_act(x1, self.norm2.weight, self.norm2.bias, in1=ff, eps=self.norm2.eps)
 
 
