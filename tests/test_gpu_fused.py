@@ -150,7 +150,7 @@ def test_norm_act_bwd_second_addend_and_colsum(cuda_device):
         y.backward(da.float() + db.float())
         assert rel_err(d_in0, x.grad) <= tol and rel_err(d_skip, sk.grad) <= tol
         assert rel_err(dg, g2.grad) <= 3e-5 and rel_err(dbt, b2.grad) <= 3e-5
-        assert rel_err(dcol, d_in0.float().sum(0)) <= 1e-5
+        assert rel_err(dcol, x.grad.sum(0)) <= 3e-5   # fp32 sums of the unrounded d_in0
 
 
 @pytest.mark.parametrize("mixer,grid", [("fft", (8, 8)), ("dwt", (8, 8)), ("permut", None)])

@@ -1,4 +1,7 @@
-python -m pytest tests/test_gpu_fused.py -m gpu -x -q 2>&1 | tail -12
-python profiles/kernel_bench.py --iters 10 --only na --match C4 > gpurun_out/kernel_bench_na.jsonl 2>&1; echo "kbench rc=$?"; cat gpurun_out/kernel_bench_na.jsonl
-python bench.py --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/bench_c4.json 2> gpurun_out/bench_c4.err; echo "bench rc=$?"; cat gpurun_out/bench_c4.json | cut -c1-300; tail -3 gpurun_out/bench_c4.err
-python tools/profile_step.py c4 > gpurun_out/step_profile_c4.txt 2>&1; echo "profile rc=$?"
+python -m pytest tests -m gpu -x -q 2>&1 | tail -6
+for c in c4 c1 c2 c3 c5; do
+python bench.py --steps 10 --warmup 3 --no-cpu-baseline --config $c > gpurun_out/bench_$c.json 2> gpurun_out/bench_$c.err; echo "bench $c rc=$?"; python -c "
+import json,sys
+d=json.load(open('gpurun_out/bench_$c.json')); print({k:d[k] for k in ('value','ms_per_step','gpu_launches','final_loss')}, d['e2e']['value'], d['roofline'] and (d['roofline']['kernel'],d['roofline']['achieved'],d['roofline']['frac']), {k:(v.get('GBps'),v['mean_ms']) for k,v in d['kernels'].items()})"; tail -2 gpurun_out/bench_$c.err
+done
+python tools/profile_step.py c4 1024 > gpurun_out/step_profile_c4.txt 2>&1; echo "profile rc=$?"

@@ -172,12 +172,12 @@ class _EncoderLayer(torch.autograd.Function):
         d_h2, d_a1, dl3w, dl3b, db3 = na_bwd(d_z, h2, l3w, l3b, mean3, rstd3, skip_shape=(rows, hid), eps=eps[2], act=1,
                                              drop_p=p2, seed=seed2, colsum=True)
         dw3 = torch.mm(d_h2.t(), a1)
-        d_a1 = torch.addmm(d_a1, d_h2, w3c)                        # skip path + GEMM path in the GEMM epilogue
+        d_a1.addmm_(d_h2, w3c)                                     # skip path + GEMM path in the GEMM epilogue (in place)
         # a1 = drop(GELU(LN(h1)) + pool_up(x1))
         d_h1, d_x1, dl1w, dl1b, db1 = na_bwd(d_a1, h1, l1w, l1b, mean2, rstd2, skip_shape=(rows, E), eps=eps[1], act=1,
                                              drop_p=p1, seed=seed1, colsum=True)
         dw1 = torch.mm(d_h1.t(), x1)
-        d_x1 = torch.addmm(d_x1, d_h1, w1c)
+        d_x1.addmm_(d_h1, w1c)
         # x1 = LN1(m) + x: upstream = d_x1 (skip + GEMM paths) + d_z (LN2 path), summed inside the kernel;
         # the identity skip hands the summed gradient on as d_x
         d_m, d_x, dn1w, dn1b, _ = na_bwd(d_x1, m.view(rows, E), n1w, n1b, mean1, rstd1, skip_shape=(rows, E), eps=eps[0],

@@ -202,6 +202,8 @@ class SpectralPatchEmbed(nn.Module):
         self.dropout = nn.Dropout(dropout)
 
     def forward(self, img: torch.Tensor) -> torch.Tensor:
+        if img.is_cuda and _FUSED_DEFAULT:
+            return self.forward_folded(img)
         batch, chans = img.shape[:2]
         P = self.P
         patches = img.unfold(2, P, P).unfold(3, P, P)                       # [B, C, nH, nW, P, P]
@@ -211,6 +213,40 @@ class SpectralPatchEmbed(nn.Module):
         spec = spec * self.freq_weight_h.view(1, 1, 1, P, 1) * self.freq_weight_w.view(1, 1, 1, 1, -1)
         tokens = self.proj(spec.permute(0, 2, 1, 3, 4).flatten(2))          # [B, N, E]
         tokens = torch.cat((self.cls_token.expand(batch, -1, -1), tokens), dim=1)
+        return self.dropout(tokens + self.position_embeddings)
+
+    def _cos_dft(self, device) -> torch.Tensor:
+        """``D[(h, w), (kh, kw)] = cos(2 pi (kh h + kw w) / P) / P``: ``Re(rfft2(p, norm="ortho")) = p_flat @ D``."""
+        D = getattr(self, "_D", None)
+        if D is None or D.device != device:
+            P, half = self.P, self.P // 2 + 1
+            h = torch.arange(P, dtype=torch.float64)
+            ang = (h.view(P, 1, 1, 1) * h.view(1, 1, P, 1) + h.view(1, P, 1, 1) * h[:half].view(1, 1, 1, half))
+            D = (torch.cos(2 * torch.pi * ang / P) / P).reshape(P * P, P * half).float().to(device)
+            self._D = D   # plain attribute: not a buffer, so state_dict keys stay the reference's
+        return D
+
+    def forward_folded(self, img: torch.Tensor) -> torch.Tensor:
+        """The same map as ONE GEMM: ``Re(rfft2)``, the frequency gains and the
+        projection are all linear in the patch, so ``tokens = patch_flat @ M + b`` with
+        ``M[(c,h,w), e] = sum_{kh,kw} D[(h,w),(kh,kw)] fwh[kh] fww[kw] Wp[e,(c,kh,kw)]`` rebuilt from the
+        parameters every call (42 MFLOP at P=16; autograd reaches all three parameters through it).  Replaces the
+        cuFFT launch, its complex -> real copy, two broadcast multiplies and a permute copy over a
+        ``[B, C, N, P, P/2+1]`` fp32 tensor by one patch-gather copy + one GEMM."""
+        batch, chans = img.shape[:2]
+        P, half = self.P, self.P // 2 + 1
+        nh, nw = img.shape[2] // P, img.shape[3] // P
+        with torch.autocast("cuda", enabled=False):
+            wf = (self.proj.weight.float().view(self.embed_dim, chans, P, half)
+                  * self.freq_weight_h.float().view(1, 1, P, 1) * self.freq_weight_w.float().view(1, 1, 1, half))
+            # [C, P*P, P*half] @ [C, P*half, E] -> [C*P*P, E]
+            M = torch.matmul(self._cos_dft(img.device), wf.view(self.embed_dim, chans, P * half).permute(1, 2, 0))
+            M = M.reshape(chans * P * P, self.embed_dim)
+        dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else img.dtype
+        patches = img[:, :, :nh * P, :nw * P].reshape(batch, chans, nh, P, nw, P).permute(0, 2, 4, 1, 3, 5)
+        flat = patches.to(dt).reshape(batch * nh * nw, chans * P * P)        # one gather copy (+ cast)
+        tokens = torch.addmm(self.proj.bias.to(dt), flat, M.to(dt)).view(batch, nh * nw, self.embed_dim)
+        tokens = torch.cat((self.cls_token.expand(batch, -1, -1).to(tokens.dtype), tokens), dim=1)
         return self.dropout(tokens + self.position_embeddings)
 
 
