@@ -137,3 +137,46 @@ class Trainer:
         loss.backward()
         self.opt.step()
         return loss.detach()
+
+
+class HostBatchPrefetcher:
+    """Double-buffered pinned-host -> device feed for ``Trainer.step`` (what a DataLoader with ``pin_memory`` plus
+    ``non_blocking`` copies amounts to, reference: ``spectre_vit/repl/train.py:147-173,214-216``): the copy of batch
+    i+1 runs on a side stream while step i computes, so every step still moves one whole batch over PCIe but the
+    transfer is off the critical path.  ``next()`` returns device tensors valid until the call after next."""
+
+    def __init__(self, device, like_img: torch.Tensor, like_lab: torch.Tensor):
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(self.device)
+        self.bufs = [(torch.empty_like(like_img, device=self.device), torch.empty_like(like_lab, device=self.device))
+                     for _ in range(2)]
+        self.ready = [torch.cuda.Event() for _ in range(2)]
+        self.consumed = [torch.cuda.Event() for _ in range(2)]
+        self.i = 0          # index of the next batch handed out
+        self.staged = 0     # number of batches whose copy has been enqueued
+        for e in self.consumed:
+            e.record(torch.cuda.current_stream(self.device))
+
+    def stage(self, himg: torch.Tensor, hlab: torch.Tensor) -> None:
+        """Enqueue the H2D copy of one (pinned) host batch on the side stream."""
+        b = self.staged & 1
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(self.consumed[b])
+            self.bufs[b][0].copy_(himg, non_blocking=True)
+            self.bufs[b][1].copy_(hlab, non_blocking=True)
+            self.ready[b].record(self.stream)
+        self.staged += 1
+
+    def next(self):
+        """Device tensors of the oldest staged batch (the compute stream waits for its copy)."""
+        if self.i >= self.staged:
+            raise RuntimeError("HostBatchPrefetcher.next(): nothing staged")
+        b = self.i & 1
+        torch.cuda.current_stream(self.device).wait_event(self.ready[b])
+        self.i += 1
+        return self.bufs[b]
+
+    def release(self) -> None:
+        """Mark the batch returned by the last ``next()`` as consumed (call after the step was enqueued)."""
+        self.consumed[(self.i - 1) & 1].record(torch.cuda.current_stream(self.device))
+
