@@ -1,7 +1,3 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -6
-for c in c4 c1 c2 c3 c5; do
-python bench.py --steps 10 --warmup 3 --no-cpu-baseline --config $c > gpurun_out/bench_$c.json 2> gpurun_out/bench_$c.err; echo "bench $c rc=$?"; python -c "
-import json,sys
-d=json.load(open('gpurun_out/bench_$c.json')); print({k:d[k] for k in ('value','ms_per_step','gpu_launches','final_loss')}, d['e2e']['value'], d['roofline'] and (d['roofline']['kernel'],d['roofline']['achieved'],d['roofline']['frac']), {k:(v.get('GBps'),v['mean_ms']) for k,v in d['kernels'].items()})"; tail -2 gpurun_out/bench_$c.err
-done
-python tools/profile_step.py c4 1024 > gpurun_out/step_profile_c4.txt 2>&1; echo "profile rc=$?"
+python -m pytest tests/test_gpu_fused.py -m gpu -x -q 2>&1 | tail -3
+python profiles/kernel_bench.py --iters 10 --only na --match C4 > gpurun_out/kernel_bench_na.jsonl 2>&1; echo "kbench rc=$?"; cut -c1-200 gpurun_out/kernel_bench_na.jsonl
+ncu --set full --clock-control none --import-source on -k regex:norm_act -c 4 -o gpurun_out/ncu_normact -f python profiles/kernel_bench.py --iters 1 --only na --match "C4 GELU(LN(h1))+up N1536" > gpurun_out/ncu_na.log 2>&1; echo "ncu rc=$?"; tail -2 gpurun_out/ncu_na.log

@@ -115,11 +115,12 @@ constexpr MatImage<H, W> make_mats() {
         const double c = cos2pi((kw * k) % W, W), s = sin2pi((kw * k) % W, W);
         m.w[(C::kOffB1 + bmat_off(n, k, 16)) / 2] = bf16_bits(n % 2 == 0 ? c : -s);
       }
-      // B4[n = w][k = 2*slot(kw)+ri]: C2R along W with the Hermitian weights folded in
+      // B4[n = w][k = 2*slot(kw)+ri]: C2R along W with the Hermitian weights and 1/(H*W) folded in
       const int kw4 = C::kw_of_slot(k / 2);
       if (kw4 >= 0 && n < W) {
         const double c = cos2pi((kw4 * n) % W, W), s = sin2pi((kw4 * n) % W, W);
-        const double wgt = (kw4 == 0 || (W % 2 == 0 && kw4 == W / 2)) ? 1.0 : 2.0;
+        // Hermitian weight and the ortho scale 1/(H*W) of the whole rfft2 -> irfft2 round trip
+        const double wgt = ((kw4 == 0 || (W % 2 == 0 && kw4 == W / 2)) ? 1.0 : 2.0) / static_cast<double>(H * W);
         m.w[(C::kOffB4 + bmat_off(n, k, 16)) / 2] = bf16_bits(k % 2 == 0 ? wgt * c : -wgt * s);
       }
     }
@@ -223,17 +224,14 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
   if (warp < 8) {
     const int g = warp >> 2, c = c0 + (warp & 3) * 32 + lane;
     const bool cvalid = c < p.E;
-    const float scale = 1.0f / static_cast<float>(H * W);
     const float2* fp = reinterpret_cast<const float2*>(p.filt) + (cvalid ? c : 0);
 #pragma unroll
     for (int j = 0; j < KWG; ++j) {
       const int kw = g * KWG + j;
       const bool ok = kw < WH && cvalid;
 #pragma unroll
-      for (int kh = 0; kh < H; ++kh) {
-        const float2 f = __ldg(fp + (ok ? (static_cast<size_t>(kh) * WH + kw) * p.E : 0));   // branch-free
-        Fld[j][kh] = ok ? make_float2(f.x * scale, f.y * scale) : make_float2(0.f, 0.f);
-      }
+      for (int kh = 0; kh < H; ++kh)   // branch-free, and no arithmetic on the values: the loads stay in flight
+        Fld[j][kh] = __ldg(fp + (ok ? (static_cast<size_t>(kh) * WH + kw) * p.E : 0));
     }
   }
   for (int i = tid; i < C::kMatBytes / 16; i += kThreads)
@@ -263,7 +261,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     const uint32_t tD = tbase + lane_off + C::kDCol;
     const uint32_t tA = tbase + lane_off + C::kACol;
 
-    // filter slice of this thread, pre-scaled by the ortho 1/(H*W): bins kh < 8 of kw = g*KWG + j
+    // filter slice of this thread (the ortho 1/(H*W) lives in the C2R matrix): bins kh < 8 of kw = g*KWG + j
     // stay in registers, bins kh >= 8 are parked in spare TMEM columns of the thread's own lane
     // (16 columns per kw, read back next to the D2 loads) - 112 live filter registers would spill.
     // (The global loads were issued before the setup barrier; see `Fld` above.)
@@ -761,15 +759,12 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
     }
     SB200_STAMP(5, 0, 1);
   }
-  for (int i = tid; i < C::kMatBytes / 16; i += kThreads)
-    reinterpret_cast<uint4*>(sMat)[i] = reinterpret_cast<const uint4*>(g_mats<H, W>.w)[i];
-  if (tid == 0) SB200_STAMP(5, 0, 2);
   {
-    // conj(filt) / (H*W) of this CTA's 64 channels: sF[c][slot][kh][re,im], channel stride padded.
-    // All global loads are issued before the first shared-memory store (memory-level parallelism:
-    // a load->store loop would serialise ~20 DRAM round trips per thread).
-    const float scale = 1.0f / static_cast<float>(H * W);
+    // conj(filt) of this CTA's 64 channels: sF[c][slot][kh][re,im], channel stride padded (the ortho 1/(H*W) lives
+    // in the C2R matrix).  All global loads -- filter and DFT matrices -- are issued before the first shared-memory
+    // store (memory-level parallelism: a load->store loop would serialise ~20 DRAM round trips per thread).
     constexpr int kIters = (64 * 8 * H + kThreads - 1) / kThreads;
+    constexpr int kMatIters = (C::kMatBytes / 16 + kThreads - 1) / kThreads;
     float2 fv[kIters];
 #pragma unroll
     for (int k = 0; k < kIters; ++k) {
@@ -782,14 +777,25 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
       const float2 f = __ldg(reinterpret_cast<const float2*>(p.filt) + off);
       fv[k] = ok ? f : make_float2(0.f, 0.f);
     }
+    uint4 mv[kMatIters];
+#pragma unroll
+    for (int k = 0; k < kMatIters; ++k) {
+      const int i = tid + k * kThreads;
+      mv[k] = reinterpret_cast<const uint4*>(g_mats<H, W>.w)[i < C::kMatBytes / 16 ? i : 0];
+    }
+    if (tid == 0) SB200_STAMP(5, 0, 2);
+#pragma unroll
+    for (int k = 0; k < kMatIters; ++k) {
+      const int i = tid + k * kThreads;
+      if (i < C::kMatBytes / 16) reinterpret_cast<uint4*>(sMat)[i] = mv[k];
+    }
     if (tid == 0) SB200_STAMP(5, 0, 3);
 #pragma unroll
     for (int k = 0; k < kIters; ++k) {
       const int i = tid + k * kThreads;
       const int cl = i & 63, rest = i >> 6, s = rest / H, kh = rest % H;
       if (i < 64 * 8 * H)
-        *reinterpret_cast<float2*>(sF + cl * SM::kFiltStride + s * SM::kSlotF + kh * 2) =
-            make_float2(fv[k].x * scale, -fv[k].y * scale);
+        *reinterpret_cast<float2*>(sF + cl * SM::kFiltStride + s * SM::kSlotF + kh * 2) = make_float2(fv[k].x, -fv[k].y);
     }
     if (tid == 0) SB200_STAMP(5, 0, 4);
     for (int i = tid; i < 64 * 4; i += kThreads) sF[(i >> 2) * SM::kFiltStride + 8 * SM::kSlotF + (i & 3)] = 0.f;
@@ -883,7 +889,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
               if (kh < H) {
                 const float dr = f32(vd[2 * qq]), di = f32(vd[2 * qq + 1]);
                 const float xr = f32(vx[2 * qq]), xi = f32(vx[2 * qq + 1]);
-                const float fr = (qq & 1) ? f4[qq >> 1].z : f4[qq >> 1].x;   // already conj(filt)/(H*W)
+                const float fr = (qq & 1) ? f4[qq >> 1].z : f4[qq >> 1].x;   // already conj(filt)
                 const float fi = (qq & 1) ? f4[qq >> 1].w : f4[qq >> 1].y;
                 if (mvalid) {
                   float2& a = acc[hf][e][kh < H ? kh : 0];

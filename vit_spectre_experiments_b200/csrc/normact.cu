@@ -191,15 +191,20 @@ __device__ __forceinline__ void row_sum(float (&v)[NV], float (*red)[NV][8], int
 #pragma unroll
     for (int i = 0; i < NV; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
   if (wpr > 1) {
-    const int w = threadIdx.x >> 5;
-    if ((threadIdx.x & 31) == 0)
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0)
 #pragma unroll
       for (int i = 0; i < NV; ++i) red[slot][i][w] = v[i];
     __syncthreads();
+    // wpr <= 8 partials per row: lane (l & 7) fetches one, three butterfly steps leave the sum in every lane
+    // (branch-free; a runtime-length loop here compiled to ~60 instructions of remainder handling)
+    const int k = lane & 7;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
-      float s = 0.f;
-      for (int k = 0; k < wpr; ++k) s += red[slot][i][rg * wpr + k];
+      float s = k < wpr ? red[slot][i][rg * wpr + k] : 0.f;
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      s += __shfl_xor_sync(0xffffffffu, s, 4);
       v[i] = s;
     }
   }
@@ -648,10 +653,13 @@ static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, 
   while (sh.rpc > 1 && sh.rpc * row_bytes > 48 * 1024) sh.rpc /= 2;
   if (sh.rpc < 1) sh.rpc = 1;
   sh.stage_bytes = (sh.rpc * row_bytes + 127) / 128 * 128;
-  sh.stages = (bwd ? 36 : 64) * 1024 / sh.stage_bytes;
+  // ring depth: whatever keeps three CTAs resident (~74 KB each) next to the backward's accumulators
+  const size_t fixed = bwd ? static_cast<size_t>(nacc * sh.rpc + 2) * N * sizeof(float) : 0;
+  const long long room = 74 * 1024 - static_cast<long long>(fixed);
+  sh.stages = room > 0 ? static_cast<int>(room / sh.stage_bytes) : 0;
   if (sh.stages < 2) sh.stages = 2;
   if (sh.stages > kMaxStages) sh.stages = kMaxStages;
-  sh.smem = static_cast<size_t>(sh.stages) * sh.stage_bytes + (bwd ? static_cast<size_t>(nacc * sh.rpc + 2) * N * sizeof(float) : 0);
+  sh.smem = static_cast<size_t>(sh.stages) * sh.stage_bytes + fixed;
   return sh;
 }
 
