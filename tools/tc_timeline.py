@@ -57,3 +57,9 @@ for who in range(WHO):
         if any(v is not None for v in vals):
             d = [vals[i] - vals[i - 1] if i and vals[i] is not None and vals[i - 1] is not None else 0 for i in range(len(vals))]
             print(f"{names[who]:7s} tile{t}: start {vals[0]} deltas " + " ".join(str(x) for x in d[1:]))
+for t, name in ((0, "CTA 0"), (1, "last CTA")):
+    q = p[4, t]
+    ns, clk = int(q[1]) - int(q[0]), int(q[3]) - int(q[2])
+    if ns > 0:
+        print(f"{name}: wall {ns / 1e3:.1f} us, {clk} clk => SM clock {clk / ns * 1e3:.0f} MHz; started {int(q[0]) - int(p[4, 0, 0])} ns after CTA 0")
+

@@ -44,6 +44,25 @@ constexpr int kProfStamps = 16, kProfTiles = 8;
       p.prof[((who) * kProfTiles + (tile)) * kProfStamps + (idx)] = clock64();                  \
   } while (0)
 
+
+// wall-clock stamps (debug, -DSB200_WALLCLOCK=1): %globaltimer + clock64 at entry / exit of CTA 0 and of the last CTA
+#ifndef SB200_WALLCLOCK
+#define SB200_WALLCLOCK 0
+#endif
+__device__ __forceinline__ long long global_ns() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define SB200_WALL(slot)                                                                         \
+  do {                                                                                          \
+    if (SB200_WALLCLOCK && p.prof && threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) { \
+      long long* q = p.prof + ((4 * kProfTiles + (blockIdx.x == 0 ? 0 : 1)) * kProfStamps);     \
+      q[(slot)] = global_ns();                                                                  \
+      q[(slot) + 2] = clock64();                                                                \
+    }                                                                                           \
+  } while (0)
+
 constexpr int kEpiThreads = 256;
 constexpr int kThreads = 384;
 constexpr int kBarCount = kEpiThreads + 32;  // named barriers: epilogue arrives, MMA warp syncs
@@ -194,6 +213,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
   __shared__ __align__(16) uint8_t sDummy[8 * 16];   // sink for the padded rows of stmatrix
 
   const long long t_start = clock64();
+  SB200_WALL(0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ct = blockIdx.x % p.nct;
   const int img0 = blockIdx.x / p.nct;
@@ -566,6 +586,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
   }
   tc_fence_before_sync();
   __syncthreads();
+  SB200_WALL(1);
   if (warp == 8) tmem_dealloc<512>(tbase);
 }
 
@@ -727,6 +748,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
   __shared__ __align__(16) uint8_t sDummy[8 * 16];
 
   const long long t_start = clock64();
+  SB200_WALL(0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int cb = blockIdx.x % p.nblk;
   const int pair0 = blockIdx.x / p.nblk;
@@ -1174,6 +1196,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
   }
   tc_fence_before_sync();
   __syncthreads();
+  SB200_WALL(1);
   if (warp == 8) tmem_dealloc<512>(tbase);
 }
 
