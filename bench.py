@@ -141,7 +141,7 @@ def main():
     cfg = load_named(args.config)
     rank, local_rank, world = dist_env()
     batch = args.batch or getattr(cfg, "bench_batch_size", cfg.batch_size)
-    cpu_batch = args.cpu_batch or {"c4": 16, "c5": 4, "c3": 64, "c1": 64, "c2": 512}[args.config]
+    cpu_batch = args.cpu_batch or {"c4": 64, "c5": 16, "c3": 256, "c1": 256, "c2": 2048}[args.config]   # ~10-20 s of CPU work
     grid = cfg.img_size // cfg.patch_size
     T, E, L = grid * grid + 1, cfg.embed_dim, cfg.num_encoders
     config = {"workload": WORKLOADS[args.config], "name": args.config, "mixer": cfg.mixer, "grid": f"{grid}x{grid}",
@@ -273,7 +273,7 @@ def main():
                     "traffic": traffic.get(f"{args.config}:{key}")}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            cpu, _ = cpu_reference_leg(cfg, 2, 1, cpu_batch, args.config)
+            cpu, _ = cpu_reference_leg(cfg, 3, 1, cpu_batch, args.config)
         out = {
             "metric": METRIC, "value": round(batch * world * K / (ms_total / 1e3), 1), "unit": "images/s",
             "n_gpus": world, "steps": K, "warmup": warm, "ms_per_step": round(ms_total / K, 3),

@@ -180,3 +180,26 @@ def test_encoder_layer_fused_matches_torch(cuda_device, autocast, mixer, grid):
     pa, pb = dict(a.named_parameters()), dict(b.named_parameters())
     for k in pa:
         assert rel_err(pa[k].grad, pb[k].grad) <= (5e-2 if autocast else 1e-4), k
+
+
+def test_host_batch_prefetcher_feeds_the_same_batches(cuda_device):
+    """train.HostBatchPrefetcher (bench.py's end-to-end feed): double-buffered pinned-host -> device copies on a side
+    stream deliver exactly the staged batches, in order."""
+    from vit_spectre_experiments_b200.train import HostBatchPrefetcher
+
+    like_img = torch.empty(4, 3, 8, 8, device=cuda_device)
+    like_lab = torch.empty(4, dtype=torch.long, device=cuda_device)
+    feed = HostBatchPrefetcher(cuda_device, like_img, like_lab)
+    host = [(torch.full((4, 3, 8, 8), float(i)).pin_memory(), torch.full((4,), i, dtype=torch.long).pin_memory())
+            for i in range(5)]
+    feed.stage(*host[0])
+    for i in range(5):
+        img, lab = feed.next()
+        if i + 1 < 5:
+            feed.stage(*host[i + 1])
+        s = img.sum() + lab.sum()          # consumer work enqueued on the current stream
+        feed.release()
+        assert s.item() == i * 4 * 3 * 8 * 8 + i * 4
+    with pytest.raises(RuntimeError):
+        feed.next()
+

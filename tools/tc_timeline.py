@@ -24,7 +24,7 @@ f = torch.randn(H, W // 2 + 1, E, 2, device=dev)
 y, dx, df = torch.empty_like(x), torch.empty_like(x), torch.empty_like(f)
 st = torch.cuda.current_stream().cuda_stream
 WHO, TILES, STAMPS = 6, 8, 16
-prof = torch.zeros(WHO * TILES * STAMPS, dtype=torch.int64, device=dev)
+prof = torch.zeros(2048, dtype=torch.int64, device=dev)   # [0, 768): phase stamps; [1024, ...): per-CTA wall clock
 nws = lib.spectre_fftmix_bwd_workspace_bytes(B, H, W, E)
 ws = torch.empty(max(nws, 16), dtype=torch.uint8, device=dev)
 
@@ -46,7 +46,8 @@ fn(prof.data_ptr())
 run()
 torch.cuda.synchronize()
 fn(None)
-p = prof.cpu().view(WHO, TILES, STAMPS)
+pc = prof.cpu()
+p = pc[:WHO * TILES * STAMPS].view(WHO, TILES, STAMPS)
 t0 = int(p[0, 0, 14])
 print(f"setup: start=0 setup_done={int(p[0,0,15])-t0} filter_loaded={int(p[0,0,13])-t0}")
 names = {0: "epiWG0", 1: "epiWG1", 2: "mma", 3: "tma", 4: "aux4", 5: "aux5"}
@@ -62,4 +63,14 @@ for t, name in ((0, "CTA 0"), (1, "last CTA")):
     ns, clk = int(q[1]) - int(q[0]), int(q[3]) - int(q[2])
     if ns > 0:
         print(f"{name}: wall {ns / 1e3:.1f} us, {clk} clk => SM clock {clk / ns * 1e3:.0f} MHz; started {int(q[0]) - int(p[4, 0, 0])} ns after CTA 0")
+w = pc[1024:1024 + 2 * 148].view(148, 2)
+live = w[:, 0] > 0
+if live.any():
+    t00 = int(w[live, 0].min())
+    st = (w[live, 0] - t00).float() / 1e3
+    en = (w[live, 1] - t00).float() / 1e3
+    print(f"per-CTA wall clock ({int(live.sum())} CTAs): start min/max {st.min():.1f}/{st.max():.1f} us, "
+          f"end min/median/max {en.min():.1f}/{en.median():.1f}/{en.max():.1f} us")
+    worst = torch.argsort(en, descending=True)[:6]
+    print("  latest CTAs:", [(int(i), round(float(en[i]), 1)) for i in worst])
 

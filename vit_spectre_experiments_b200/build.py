@@ -50,6 +50,7 @@ def build_library(force: bool = False, packed_math: bool | None = None, verbose:
     if packed_math is None:
         packed_math = os.environ.get("SB200_PACKED_MATH", "0") == "1"
     flags.append(f"-DSB200_PACKED_MATH={1 if packed_math else 0}")
+    flags += os.environ.get("SB200_EXTRA_NVCC_FLAGS", "").split()   # e.g. -DSB200_WALLCLOCK=1 (debug stamps)
     if verbose:
         flags += ["-Xptxas", "-v"]
 

@@ -61,6 +61,7 @@ __device__ __forceinline__ long long global_ns() {
       q[(slot)] = global_ns();                                                                  \
       q[(slot) + 2] = clock64();                                                                \
     }                                                                                           \
+    if (SB200_WALLCLOCK && p.prof && threadIdx.x == 0) p.prof[1024 + 2 * blockIdx.x + (slot)] = global_ns(); \
   } while (0)
 
 constexpr int kEpiThreads = 256;
