@@ -113,6 +113,18 @@ int spectre_norm_act_fwd(const spectre_norm_act_t* desc, void* stream);
 int spectre_norm_act_bwd(const spectre_norm_act_t* desc, void* stream);
 size_t spectre_norm_act_bwd_workspace_bytes(long long rows, int N);
 
+/* ---------------------------------------------------------------------------------------------------
+ * MHPermutMix gather -- the reference's HEAD occupant of the slot (spectre_vit/models/spectre/layers.py:68-70):
+ *   mixed[b, h, j] = x.view(B, T*E)[b, perms[h, j]] * signs[h, j]            -> [B, heads, F], F = T*E
+ * perms: int64 [heads, F] (each row a permutation, layers.py:61-64); signs: float32 [heads, F] (+-1).
+ * Backward takes the inverse permutations inv[h, perms[h, j]] = j:
+ *   dx[b, i] = sum_h dmixed[b, h, inv[h, i]] * signs[h, inv[h, i]]            (heads summed in a fixed order)
+ * x / out / dout / dx share act_dtype; F must be a multiple of 4; all pointers 16-byte aligned. */
+int spectre_permut_fwd(const void* x, const long long* perms, const float* signs, void* out,
+                       int B, long long F, int heads, int act_dtype, void* stream);
+int spectre_permut_bwd(const void* dout, const long long* inv_perms, const float* signs, void* dx,
+                       int B, long long F, int heads, int act_dtype, void* stream);
+
 /* 1 if (H, W) has a compiled FFT-mixer kernel, else 0. */
 int spectre_fftmix_supported(int H, int W);
 

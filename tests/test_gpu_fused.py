@@ -203,3 +203,32 @@ def test_host_batch_prefetcher_feeds_the_same_batches(cuda_device):
     with pytest.raises(RuntimeError):
         feed.next()
 
+
+@pytest.mark.parametrize("B,T,E,heads,dtype", [(8, 65, 512, 16, torch.float32), (3, 50, 48, 8, torch.float32),
+                                               (37, 17, 24, 3, torch.bfloat16), (1, 5, 4, 1, torch.float32)])
+def test_permut_mix_gather(cuda_device, B, T, E, heads, dtype):
+    """MHPermutMix gather kernels (C ABI ``spectre_permut_*``; layers.py:68-70): forward bit-identical to
+    ``x.view(B,-1)[:, perms] * signs``; backward (inverse-permutation gather, heads summed in a fixed order) matches
+    torch's index backward to fp32 rounding and is bit-reproducible."""
+    from vit_spectre_experiments_b200.functional import inverse_permutations, permut_mix
+
+    g = torch.Generator().manual_seed(B * 100 + heads)
+    F_ = T * E
+    perms = torch.stack([torch.randperm(F_, generator=g) for _ in range(heads)]).to(cuda_device)
+    signs = (torch.randint(0, 2, (1, heads, F_), generator=g, dtype=torch.float32) * 2 - 1).to(cuda_device)
+    x = torch.randn(B, T, E, generator=g).to(dtype).to(cuda_device)
+    inv = inverse_permutations(perms)
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    ya = permut_mix(xa, perms, signs, inv)
+    yb = (xb.reshape(B, -1)[:, perms] * signs).to(dtype)
+    assert ya.shape == (B, heads, F_) and ya.dtype == dtype and torch.equal(ya, yb)
+    w = torch.randn(B, heads, F_, generator=g).to(dtype).to(cuda_device)
+    ya.backward(w)
+    yb.backward(w)
+    assert rel_err(xa.grad, xb.grad) <= (2e-6 if dtype == torch.float32 else 1e-2)
+    xc = x.clone().requires_grad_(True)
+    permut_mix(xc, perms, signs, inv).backward(w)
+    assert torch.equal(xc.grad, xa.grad)
+    with pytest.raises(RuntimeError):
+        inverse_permutations(torch.zeros(2, 8, dtype=torch.int64, device=cuda_device))
+

@@ -1,3 +1,2 @@
-python -m pytest tests/test_gpu_fused.py -m gpu -x -q 2>&1 | tail -3
-python profiles/kernel_bench.py --iters 10 --only na --match C4 > gpurun_out/kernel_bench_na.jsonl 2>&1; echo "kbench rc=$?"; cut -c1-200 gpurun_out/kernel_bench_na.jsonl
-ncu --set full --clock-control none --import-source on -k regex:norm_act -c 4 -o gpurun_out/ncu_normact -f python profiles/kernel_bench.py --iters 1 --only na --match "C4 GELU(LN(h1))+up N1536" > gpurun_out/ncu_na.log 2>&1; echo "ncu rc=$?"; tail -2 gpurun_out/ncu_na.log
+python -m pytest tests -m gpu -x -q 2>&1 | tail -8
+python bench.py --steps 10 --warmup 3 --config c1 --no-cpu-baseline 2>&1 | cut -c1-200

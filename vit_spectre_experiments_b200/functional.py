@@ -157,6 +157,67 @@ class _Mix(torch.autograd.Function):
         return dx, dparam, None, None, None, None
 
 
+class _PermutMix(torch.autograd.Function):
+    """``x.view(B, -1)[:, perms] * signs`` (layers.py:68-70) through ``spectre_permut_fwd`` / ``_bwd``."""
+
+    @staticmethod
+    def forward(ctx, x, perms, signs, inv):
+        lib = _lib.load()
+        code = _act_code(x, "permut_mix")
+        x = x.contiguous()
+        B = x.shape[0]
+        heads, F = perms.shape
+        if x.numel() != B * F:
+            raise RuntimeError(f"permut_mix: x has {x.numel() // B} elements per image, perms index {F}")
+        if perms.dtype != torch.int64 or signs.dtype != torch.float32 or signs.numel() != heads * F:
+            raise RuntimeError("permut_mix: perms must be int64 [heads, T*E], signs float32 [heads, T*E]")
+        out = torch.empty(B, heads, F, dtype=x.dtype, device=x.device)
+        with torch.cuda.device(x.device):
+            with _timed("permut_fwd", (B, heads, F, x.element_size())):
+                rc = lib.spectre_permut_fwd(x.data_ptr(), perms.data_ptr(), signs.data_ptr(), out.data_ptr(), B, F, heads,
+                                            code, _stream_ptr(x.device))
+        _lib.check(rc, "spectre_permut_fwd")
+        _lib.count_launches()
+        ctx.save_for_backward(inv, signs)
+        ctx.shape = x.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _lib.load()
+        inv, signs = ctx.saved_tensors
+        heads, F = inv.shape
+        dout = dout.contiguous()
+        B = dout.shape[0]
+        dx = torch.empty(ctx.shape, dtype=dout.dtype, device=dout.device)
+        with torch.cuda.device(dout.device):
+            with _timed("permut_bwd", (B, heads, F, dout.element_size())):
+                rc = lib.spectre_permut_bwd(dout.data_ptr(), inv.data_ptr(), signs.data_ptr(), dx.data_ptr(), B, F, heads,
+                                            _act_code(dout, "permut_mix"), _stream_ptr(dout.device))
+        _lib.check(rc, "spectre_permut_bwd")
+        _lib.count_launches()
+        return dx, None, None, None
+
+
+def permut_mix(x: torch.Tensor, perms: torch.Tensor, signs: torch.Tensor, inv_perms: torch.Tensor) -> torch.Tensor:
+    """``(x.view(B, -1)[:, perms] * signs)`` -> ``[B, heads, T*E]`` in x's dtype (the sign flip is exact).
+
+    perms int64 ``[heads, T*E]`` with permutation rows, signs float32 ``[heads, T*E]`` (or ``[1, heads, T*E]``),
+    inv_perms the row-wise inverse permutations (``inverse_permutations(perms)``)."""
+    return _PermutMix.apply(x, perms.contiguous(), signs.reshape(perms.shape).contiguous(), inv_perms.contiguous())
+
+
+def inverse_permutations(perms: torch.Tensor) -> torch.Tensor:
+    """Row-wise inverse of ``perms [heads, F]``; raises if a row is not a permutation of ``range(F)``."""
+    heads, F = perms.shape
+    ar = torch.arange(F, device=perms.device, dtype=perms.dtype).expand(heads, F)
+    inv = torch.full_like(perms, -1)
+    inv.scatter_(1, perms, ar)
+    if bool((inv < 0).any()) or int(perms.min()) < 0 or int(perms.max()) >= F:
+        raise RuntimeError("permut_mix: every row of perms must be a permutation of range(T*E)")
+    return inv
+
+
 def fft_mix(x: torch.Tensor, filt: torch.Tensor, grid, has_cls: bool = True) -> torch.Tensor:
     """``cat(cls, irfft2(rfft2(x_grid, ortho) * filt, ortho))`` in one fused CUDA pass.
 

@@ -74,9 +74,24 @@ class MHPermutMix(nn.Module):
         self.register_buffer("perms", torch.stack([torch.randperm(flat) for _ in range(num_heads)]))
         self.linear = SpectreLinear(self.concat_dim, out_channels)
 
+    def _inverse(self) -> torch.Tensor:
+        """Inverse permutations for the CUDA backward (plain attribute: not part of ``state_dict``)."""
+        inv = getattr(self, "_inv", None)
+        if inv is None or inv.device != self.perms.device or getattr(self, "_inv_of", None) is not self.perms:
+            from .functional import inverse_permutations
+
+            inv = inverse_permutations(self.perms)
+            self._inv, self._inv_of = inv, self.perms
+        return inv
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         batch = x.shape[0]
-        mixed = x.reshape(batch, -1)[:, self.perms] * self.signs
+        if x.is_cuda and _FUSED_DEFAULT and x.dtype in (torch.float32, torch.bfloat16) and (self.perms.shape[1] % 4 == 0):
+            from .functional import permut_mix   # gather kernel (bit-identical forward, deterministic backward)
+
+            mixed = permut_mix(x, self.perms, self.signs, self._inverse())
+        else:
+            mixed = x.reshape(batch, -1)[:, self.perms] * self.signs
         return self.linear(mixed.view(batch, self.token_dim, self.concat_dim))
 
 
