@@ -5,7 +5,7 @@ __base__ = "default.py"
 mixer = "fft"
 precision = "bf16"
 batch_size = 256
-bench_batch_size = 1024         # per-GPU batch of bench.py: sized for 180 GB HBM3e (B=256 leaves each mixer launch at ~12 us of HBM time)
+bench_batch_size = 2048         # per-GPU batch of bench.py: sized for 180 GB HBM3e (56 GB peak); a mixer launch costs ~12 us + 2.6 / 4.2 us per tile (tools/tc_fixed_cost.py)
 val_batch_size = 256
 epochs = 300
 num_classes = 1000
