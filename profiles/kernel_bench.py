@@ -6,6 +6,7 @@ Usage: python profiles/kernel_bench.py [--iters 20] [--only fft|dwt]
 import argparse
 import json
 import os
+import re
 import sys
 
 import torch
@@ -56,15 +57,15 @@ def time_ms(fn, iters, flush):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=20)
-    ap.add_argument("--only", default="", help="fft | dwt | na")
-    ap.add_argument("--match", default="", help="substring of the shape name")
+    ap.add_argument("--only", default="", help="substring match against fft | dwt | na (e.g. fftdwt)")
+    ap.add_argument("--match", default="", help="regex searched in the shape name")
     args = ap.parse_args()
     lib = _lib.load()
     dev = torch.device("cuda:0")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     st = lambda: torch.cuda.current_stream().cuda_stream
     for name, kind, B, H, W, E, dt in SHAPES:
-        if (args.only and args.only != kind) or (args.match and args.match not in name):
+        if (args.only and kind not in args.only) or (args.match and not re.search(args.match, name)):
             continue
         T = H * W + 1
         s = 4 if dt == torch.float32 else 2
@@ -97,7 +98,7 @@ def main():
                 "workspace_MB": round(nws / 1e6, 2),
             }), flush=True)
 
-    if args.only in ("", "na"):
+    if args.only == "" or "na" in args.only:
         norm_act_bench(args, dev, flush)
 
 
@@ -117,7 +118,7 @@ def norm_act_bench(args, dev, flush):
     from vit_spectre_experiments_b200.fused import norm_act
 
     for name, rows, N, Ns, has_in1, act, p, dt in NA_SHAPES:
-        if args.match and args.match not in name:
+        if args.match and not re.search(args.match, name):
             continue
         s = 4 if dt == torch.float32 else 2
         in0 = torch.randn(rows, N, device=dev).to(dt).requires_grad_(True)
