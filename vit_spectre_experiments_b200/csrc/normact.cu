@@ -130,11 +130,11 @@ __device__ __forceinline__ float ex2_approx(float x) {
 __device__ __forceinline__ float norm_cdf(float x, float* gauss) {
   const float t = rcp_approx(fmaf(0.3275911f * 0.70710678118654752f, fabsf(x), 1.0f));
   const float e = ex2_approx(x * x * -0.72134752044448170f);     // exp(-x^2 / 2)
-  float poly = fmaf(1.061405429f, t, -1.453152027f);
-  poly = fmaf(poly, t, 1.421413741f);
-  poly = fmaf(poly, t, -0.284496736f);
-  poly = fmaf(poly, t, 0.254829592f);
-  const float half_tail = 0.5f * poly * t * e;        // 0.5 * erfc(|x| / sqrt 2)
+  float poly = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);   // coefficients pre-halved
+  poly = fmaf(poly, t, 0.5f * 1.421413741f);
+  poly = fmaf(poly, t, 0.5f * -0.284496736f);
+  poly = fmaf(poly, t, 0.5f * 0.254829592f);
+  const float half_tail = poly * (t * e);             // 0.5 * erfc(|x| / sqrt 2)
   *gauss = e;
   return x >= 0.f ? 1.0f - half_tail : half_tail;
 }
@@ -149,8 +149,8 @@ __device__ __forceinline__ float gelu_grad(float x) {
 }
 
 // counter-based dropout.  A vector of 8 columns shares one well-mixed 32-bit word (lowbias32 of the vector
-// index under the row seed); element e takes one more odd multiply + xorshift of it, and is kept iff the
-// result >= drop_p * 2^32.  Forward, backward and the general-pool transpose all go through keep().
+// index under the row seed); element e takes one more odd multiply of it, and is kept iff the
+// result >= drop_p * 2^32.  Forward and backward both go through keep_e().
 __device__ __forceinline__ unsigned vec_hash(unsigned seed, unsigned vec) {
   unsigned x = vec ^ seed;
   x ^= x >> 16; x *= 0x7feb352du;
@@ -160,18 +160,7 @@ __device__ __forceinline__ unsigned vec_hash(unsigned seed, unsigned vec) {
 }
 __device__ __forceinline__ bool keep_e(unsigned vh, int e, unsigned thresh) {
   constexpr unsigned kMul[8] = {0x9E3779B1u, 0x85EBCA77u, 0xC2B2AE3Du, 0x27D4EB2Fu, 0x165667B1u, 0xD3A2646Du, 0xFD7046C5u, 0xB55A4F09u};
-  unsigned x = vh * kMul[e];
-  x ^= x >> 15;
-  return x >= thresh;
-}
-__device__ __forceinline__ bool keep(unsigned seed, unsigned idx, unsigned thresh) {
-  const unsigned vh = vec_hash(seed, idx >> 3);
-  unsigned x = vh;
-  switch (idx & 7) {
-    case 0: return keep_e(x, 0, thresh); case 1: return keep_e(x, 1, thresh); case 2: return keep_e(x, 2, thresh);
-    case 3: return keep_e(x, 3, thresh); case 4: return keep_e(x, 4, thresh); case 5: return keep_e(x, 5, thresh);
-    case 6: return keep_e(x, 6, thresh); default: return keep_e(x, 7, thresh);
-  }
+  return vh * kMul[e] >= thresh;   // the comparison is decided by the high bits: no further mixing needed
 }
 // seed of a row: folds the high bits of the 64-bit seed and the row index so idx can stay 32-bit (column)
 __device__ __forceinline__ unsigned row_seed(const Args& a, long long row) {
@@ -210,14 +199,43 @@ __device__ __forceinline__ void row_sum(float (&v)[NV], float (*red)[NV][8], int
   }
 }
 
-// adaptive average pool Ns -> N (torch semantics), general widths: value for output column j
+// adaptive average pool Ns -> N (torch semantics), general widths.  Output column j averages the skip columns
+// [floor(j Ns / N), ceil((j+1) Ns / N)); skip column c feeds exactly the outputs [floor(c N / Ns), ceil((c+1) N / Ns)).
+// Both maps are tabulated once per CTA in shared memory (first | count << 16), so the row loop has no divisions.
+__device__ __forceinline__ void pool_windows(unsigned* tab, int n_out, int n_in) {
+  for (int j = threadIdx.x; j < n_out; j += blockDim.x) {
+    const int s = static_cast<int>((static_cast<long long>(j) * n_in) / n_out);
+    const int e = static_cast<int>((static_cast<long long>(j + 1) * n_in + n_out - 1) / n_out);
+    tab[j] = static_cast<unsigned>(s) | static_cast<unsigned>(e - s) << 16;
+  }
+}
+// o[0..8) += pool(skip)[j0 .. j0+8)
 template <class T>
-__device__ __forceinline__ float pool_general(const T* srow, int j, int N, int Ns) {
-  const int s = static_cast<int>((static_cast<long long>(j) * Ns) / N);
-  const int e = static_cast<int>((static_cast<long long>(j + 1) * Ns + N - 1) / N);
-  float acc = 0.f;
-  for (int i = s; i < e; ++i) acc += ld1(srow + i);
-  return acc / static_cast<float>(e - s);
+__device__ __forceinline__ void skip_general_add(const T* srow, const unsigned* win, int j0, float (&o)[8]) {
+  const uint4 wa = *reinterpret_cast<const uint4*>(win + j0), wb = *reinterpret_cast<const uint4*>(win + j0 + 4);
+  const unsigned w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int s = static_cast<int>(w[e] & 0xffffu), n = static_cast<int>(w[e] >> 16);
+    float acc = ld1(srow + s);
+    for (int k = 1; k < n; ++k) acc += ld1(srow + s + k);
+    o[e] = fmaf(acc, rcp_approx(static_cast<float>(n)), o[e]);
+  }
+}
+// d_skip[c0 .. c0+8) of one row from the row's window-normalised gradients dn[j] = d[j] / len(j) (shared memory)
+template <class T>
+__device__ __forceinline__ void skip_general_bwd(T* drow, const float* dn, const unsigned* cov, int c0) {
+  const uint4 wa = *reinterpret_cast<const uint4*>(cov + c0), wb = *reinterpret_cast<const uint4*>(cov + c0 + 4);
+  const unsigned w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+  float g[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int s = static_cast<int>(w[e] & 0xffffu), n = static_cast<int>(w[e] >> 16);
+    float acc = dn[s];
+    for (int k = 1; k < n; ++k) acc += dn[s + k];
+    g[e] = acc;
+  }
+  st8(drow + c0, g);
 }
 
 // o[0..8) += pool(skip)[j0 .. j0+8) for integer ratios resolved at compile time
@@ -272,7 +290,7 @@ template <class T, int VPT, int MODE, int ACT>
 __global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
   extern __shared__ __align__(128) uint8_t ring[];
   __shared__ uint64_t full[kMaxStages];
-  __shared__ float red[2][1][8];
+  __shared__ float red[2][2][8];
   const int tpr = a.tpr, wpr = tpr >> 5;
   const int rg = threadIdx.x / tpr, t = threadIdx.x - rg * tpr;
   const int nvec = a.N >> 3, S = a.stages;
@@ -284,6 +302,8 @@ __global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
   const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
   const int off_in1 = a.rpc * a.N * static_cast<int>(sizeof(T));
   const int off_skip = off_in1 * (a.in1 ? 2 : 1);
+  unsigned* win = reinterpret_cast<unsigned*>(ring + S * a.stage_bytes);   // general widths: pooling windows [N]
+  if constexpr (MODE == kSkipGeneral) pool_windows(win, a.N, a.Ns);
 
   auto issue = [&](int it, int stg) {   // one thread: the group's rows are contiguous in every operand
     const long long row0 = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc;
@@ -314,7 +334,14 @@ __global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
     const uint8_t* st = ring + stg * a.stage_bytes;
     const T* r0 = reinterpret_cast<const T*>(st) + rg * a.N;
     float z[VPT][8];
-    float s[1] = {0.f};
+    // one pass: sum and sum of squares about a pivot taken from the row itself (its first element), which keeps
+    // the E[d^2] - E[d]^2 form free of cancellation; one cross-thread reduction instead of two
+    float pivot = 0.f;
+    if (live) {
+      pivot = ld1(r0);
+      if (a.in1) pivot += ld1(reinterpret_cast<const T*>(st + off_in1) + rg * a.N);
+    }
+    float s[2] = {0.f, 0.f};
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
       const int v = t + i * tpr;
@@ -327,26 +354,22 @@ __global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
           for (int e = 0; e < 8; ++e) z[i][e] += w[e];
         }
 #pragma unroll
-        for (int e = 0; e < 8; ++e) s[0] += z[i][e];
+        for (int e = 0; e < 8; ++e) {
+          const float d = z[i][e] - pivot;
+          s[0] += d;
+          s[1] = fmaf(d, d, s[1]);
+        }
       } else {
 #pragma unroll
         for (int e = 0; e < 8; ++e) z[i][e] = 0.f;
       }
     }
-    row_sum<1>(s, red, 0, wpr, rg);
-    const float mean = s[0] * inv_n;
-    float q[1] = {0.f};
-#pragma unroll
-    for (int i = 0; i < VPT; ++i)
-      if (t + i * tpr < nvec)
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float d = z[i][e] - mean;
-          q[0] = fmaf(d, d, q[0]);
-        }
-    row_sum<1>(q, red, 1, wpr, rg);
+    row_sum<2>(s, red, it & 1, wpr, rg);
+    const float dmean = s[0] * inv_n;
+    const float mean = pivot + dmean;
+    const float var = fmaxf(fmaf(-dmean, dmean, s[1] * inv_n), 0.f);
     if (live) {
-      const float rstd = rsqrtf(q[0] * inv_n + a.eps);
+      const float rstd = rsqrtf(var + a.eps);
       if (t == 0) {
         a.mean[row] = mean;
         a.rstd[row] = rstd;
@@ -377,8 +400,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
         } else if constexpr (down_k(MODE) > 0) {
           skip_down_add<T, down_k(MODE)>(srow, j0, o);
         } else if constexpr (MODE == kSkipGeneral) {
-#pragma unroll 1
-          for (int e = 0; e < 8; ++e) o[e] += pool_general(srow, j0 + e, a.N, a.Ns);
+          skip_general_add<T>(srow, win, j0, o);
         }
         if (drop) {
           const unsigned vh = vec_hash(rseed, static_cast<unsigned>(v));
@@ -409,6 +431,11 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   const int nacc = a.nacc;                                            // 2, or 3 with the column sums of d_in0
   float* sgam = accs + a.rpc * nacc * a.N;                            // [N] gamma, [N] beta
   float* myacc = accs + rg * nacc * a.N;
+  // general skip widths: 1 / len(j) per output column [N], covering outputs per skip column [Ns], and the
+  // row group's window-normalised gradients [rpc][N]
+  float* sinv = sgam + 2 * a.N;
+  unsigned* cov = reinterpret_cast<unsigned*>(sinv + a.N);
+  float* dn = reinterpret_cast<float*>(cov + a.Ns) + rg * a.N;
   const float inv_n = 1.0f / static_cast<float>(a.N);
   const bool drop = a.drop_p > 0.f;
   const unsigned thresh = drop ? static_cast<unsigned>(fminf(a.drop_p, 0.999999f) * 4294967296.0f) : 0u;
@@ -441,6 +468,14 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
     sgam[a.N + i] = a.beta[i];
   }
   for (int i = threadIdx.x; i < a.rpc * nacc * a.N; i += blockDim.x) accs[i] = 0.f;
+  if constexpr (MODE == kSkipGeneral) {
+    pool_windows(cov, a.Ns, a.N);
+    for (int j = threadIdx.x; j < a.N; j += blockDim.x) {
+      const int s0 = static_cast<int>((static_cast<long long>(j) * a.Ns) / a.N);
+      const int e0 = static_cast<int>((static_cast<long long>(j + 1) * a.Ns + a.N - 1) / a.N);
+      sinv[j] = 1.0f / static_cast<float>(e0 - s0);
+    }
+  }
   __syncthreads();
 
   // row statistics of the first row (prefetched one iteration ahead afterwards)
@@ -502,7 +537,13 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
         skip_up_bwd<T, up_k(MODE)>(static_cast<T*>(a.d_skip) + row * a.Ns, j0, d);
       } else if constexpr (down_k(MODE) > 0) {
         skip_down_bwd<T, down_k(MODE)>(static_cast<T*>(a.d_skip) + row * a.Ns, j0, d);
-      }   // general widths: pool_bwd_general_kernel
+      } else if constexpr (MODE == kSkipGeneral) {
+        float w[8], q[8];
+        ld8(sinv + j0, w);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) q[e] = d[e] * w[e];
+        st8(dn + j0, q);     // gathered per skip column after the row sums' barrier
+      }
       // ---- main path
       float gam[8], bet[8], dg[8], db[8];
       ld8(sgam + j0, gam);
@@ -528,6 +569,11 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
       st8(myacc + a.N + j0, db);
     }
     row_sum<2>(s, red, it & 1, wpr, rg);
+    if constexpr (MODE == kSkipGeneral) {
+      if (wpr == 1) __syncwarp();   // one warp per row: dn is written and read by the same warp
+      if (live)
+        for (int u = t; u < (a.Ns >> 3); u += tpr) skip_general_bwd<T>(static_cast<T*>(a.d_skip) + row * a.Ns, dn, cov, u * 8);
+    }
     if (live) {
       const float m1 = s[0] * inv_n, m2 = s[1] * inv_n;
 #pragma unroll
@@ -560,61 +606,35 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   }
 }
 
-// general adaptive-pool transpose (only for widths that are not integer multiples): one thread per skip column
-template <class T>
-__global__ void pool_bwd_general_kernel(const Args a) {
-  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= a.rows * a.Ns) return;
-  const long long row = i / a.Ns;
-  const int c = static_cast<int>(i % a.Ns);
-  const int jlo = static_cast<int>((static_cast<long long>(c) * a.N) / a.Ns);
-  const int jhi = static_cast<int>((static_cast<long long>(c + 1) * a.N + a.Ns - 1) / a.Ns);   // exclusive
-  const bool drop = a.drop_p > 0.f;
-  const unsigned thresh = drop ? static_cast<unsigned>(fminf(a.drop_p, 0.999999f) * 4294967296.0f) : 0u;
-  const float keep_scale = drop ? 1.0f / (1.0f - a.drop_p) : 1.0f;
-  const unsigned rseed = drop ? row_seed(a, row) : 0u;
-  float acc = 0.f;
-  for (int j = jlo; j < jhi; ++j) {
-    const int s = static_cast<int>((static_cast<long long>(j) * a.Ns) / a.N);
-    const int e = static_cast<int>((static_cast<long long>(j + 1) * a.Ns + a.N - 1) / a.N);
-    if (c < s || c >= e) continue;
-    float d = ld1(static_cast<const T*>(a.dout) + row * a.N + j);
-    if (a.dout2) d += ld1(static_cast<const T*>(a.dout2) + row * a.N + j);
-    if (drop) d = keep(rseed, static_cast<unsigned>(j), thresh) ? d * keep_scale : 0.f;
-    acc += d / static_cast<float>(e - s);
-  }
-  st1(static_cast<T*>(a.d_skip) + i, acc);
-}
-
-// out_k[c] = sum_s part[s][k][c] for k < nacc (dgamma, dbeta, column sums).  CTA = 32 columns x 8 slab lanes; the
-// eight lane sums are combined in a fixed order (deterministic).
+// out_k[c] = sum_s part[s][k][c] for k < nacc (dgamma, dbeta, column sums).  CTA = 8 columns x 32 slab lanes (the
+// partials are few MB but the reduction is latency-bound: many short threads); lane sums are combined in a fixed
+// order (deterministic).
 __global__ void __launch_bounds__(256) reduce_gamma_beta_kernel(const float* __restrict__ part, float* __restrict__ dgamma,
                                                                 float* __restrict__ dbeta, float* __restrict__ dsum, int N,
                                                                 int nacc, int slabs) {
-  __shared__ float sm[8][33];
-  const int col = blockIdx.x * 32 + (threadIdx.x & 31), ln = threadIdx.x >> 5;
+  __shared__ float sm[32][9];
+  const int c8 = threadIdx.x & 7, ln = threadIdx.x >> 3;
+  const int col = blockIdx.x * 8 + c8;
   const int ncol = nacc * N;
-  float s0 = 0.f, s1 = 0.f;
+  float tot = 0.f;
   if (col < ncol) {
-    // 8 independent loads in flight per thread; partial sums are combined in a fixed order
+    // up to 8 independent loads in flight per thread (a 32-byte sector per slab row and 8 columns)
     float acc[8];
 #pragma unroll
     for (int u = 0; u < 8; ++u) acc[u] = 0.f;
-    int k = ln;
-    for (; k + 56 < slabs; k += 64) {
+    for (int k = ln; k < slabs; k += 256) {
 #pragma unroll
-      for (int u = 0; u < 8; ++u) acc[u] += part[static_cast<size_t>(k + 8 * u) * ncol + col];
+      for (int u = 0; u < 8; ++u)
+        if (k + 32 * u < slabs) acc[u] += part[static_cast<size_t>(k + 32 * u) * ncol + col];
     }
-    for (; k < slabs; k += 8) acc[0] += part[static_cast<size_t>(k) * ncol + col];
-    s0 = ((acc[0] + acc[1]) + (acc[2] + acc[3]));
-    s1 = ((acc[4] + acc[5]) + (acc[6] + acc[7]));
+    tot = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
   }
-  sm[ln][threadIdx.x & 31] = s0 + s1;
+  sm[ln][c8] = tot;
   __syncthreads();
   if (ln == 0 && col < ncol) {
     float s = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) s += sm[k][threadIdx.x];
+    for (int k = 0; k < 32; ++k) s += sm[k][c8];
     if (col < N) dgamma[col] = s;
     else if (col < 2 * N) dbeta[col - N] = s;
     else dsum[col - 2 * N] = s;
@@ -641,7 +661,7 @@ struct Shape {
   size_t smem;   // dynamic shared memory of the launch
 };
 static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, bool bwd, bool has_dout2 = false,
-                          int nacc = 2) {
+                          int nacc = 2, bool general = false) {
   Shape sh{};
   const int nvec = N / 8;
   if (nvec <= 32) { sh.vpt = 1; sh.tpr = 32; }
@@ -654,7 +674,8 @@ static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, 
   if (sh.rpc < 1) sh.rpc = 1;
   sh.stage_bytes = (sh.rpc * row_bytes + 127) / 128 * 128;
   // ring depth: whatever keeps three CTAs resident (~74 KB each) next to the backward's accumulators
-  const size_t fixed = bwd ? static_cast<size_t>(nacc * sh.rpc + 2) * N * sizeof(float) : 0;
+  size_t fixed = bwd ? static_cast<size_t>(nacc * sh.rpc + 2) * N * sizeof(float) : 0;
+  if (general) fixed += bwd ? (static_cast<size_t>(sh.rpc + 1) * N + Ns) * sizeof(float) : N * sizeof(float);
   const long long room = 74 * 1024 - static_cast<long long>(fixed);
   sh.stages = room > 0 ? static_cast<int>(room / sh.stage_bytes) : 0;
   if (sh.stages < 2) sh.stages = 2;
@@ -669,8 +690,8 @@ static int validate(const char* fn, const spectre_norm_act_t* d, bool bwd) {
   if (d->rows < 1 || d->N < 8 || (d->N % 8) || d->N > 4096)
     return fail(SPECTRE_E_SHAPE, "%s: need rows >= 1 and N a multiple of 8 in [8, 4096] (rows=%lld N=%d)", fn, d->rows, d->N);
   const bool has_skip = bwd ? d->d_skip != nullptr : d->skip != nullptr;
-  if (has_skip && (d->Ns < 1 || (d->Ns % 8)))
-    return fail(SPECTRE_E_SHAPE, "%s: skip width must be a positive multiple of 8 (Ns=%d)", fn, d->Ns);
+  if (has_skip && (d->Ns < 8 || (d->Ns % 8) || d->Ns > 16384))
+    return fail(SPECTRE_E_SHAPE, "%s: skip width must be a multiple of 8 in [8, 16384] (Ns=%d)", fn, d->Ns);
   if (d->act_dtype != SPECTRE_DTYPE_F32 && d->act_dtype != SPECTRE_DTYPE_BF16)
     return fail(SPECTRE_E_DTYPE, "%s: act_dtype=%d (0=float32, 1=bfloat16)", fn, d->act_dtype);
   if (d->drop_p < 0.f || d->drop_p >= 1.f) return fail(SPECTRE_E_SHAPE, "%s: drop_p=%g outside [0,1)", fn, d->drop_p);
@@ -750,7 +771,8 @@ int spectre_norm_act_fwd(const spectre_norm_act_t* d, void* stream) {
   if (int rc = validate("spectre_norm_act_fwd", d, false)) return rc;
   Args a = to_args(*d, false);
   const bool bf = d->act_dtype == SPECTRE_DTYPE_BF16;
-  const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, a.skip_mode != kSkipNone, bf ? 2 : 4, false);
+  const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, a.skip_mode != kSkipNone, bf ? 2 : 4, false, false, 2,
+                                a.skip_mode == kSkipGeneral);
   a.tpr = sh.tpr; a.rpc = sh.rpc; a.stages = sh.stages; a.stage_bytes = sh.stage_bytes;
   const int grid = grid_for(a.rows, sh), block = sh.tpr * sh.rpc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -780,7 +802,8 @@ int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
   if (int rc = validate("spectre_norm_act_bwd", d, true)) return rc;
   Args a = to_args(*d, true);
   const bool bf = d->act_dtype == SPECTRE_DTYPE_BF16;
-  const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, false, bf ? 2 : 4, true, a.dout2 != nullptr, a.nacc);
+  const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, false, bf ? 2 : 4, true, a.dout2 != nullptr, a.nacc,
+                                a.skip_mode == kSkipGeneral);
   a.tpr = sh.tpr; a.rpc = sh.rpc; a.stages = sh.stages; a.stage_bytes = sh.stage_bytes;
   const int grid = grid_for(a.rows, sh), block = sh.tpr * sh.rpc;
   if (!d->workspace || d->workspace_bytes < static_cast<size_t>(grid) * a.nacc * a.N * sizeof(float))
@@ -789,13 +812,7 @@ int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   table().bwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
   int launches = 1;
-  if (a.skip_mode == kSkipGeneral) {
-    const long long n = a.rows * a.Ns;
-    if (bf) pool_bwd_general_kernel<__nv_bfloat16><<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a);
-    else pool_bwd_general_kernel<float><<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a);
-    ++launches;
-  }
-  reduce_gamma_beta_kernel<<<(a.nacc * a.N + 31) / 32, 256, 0, st>>>(a.part, d->dgamma, d->dbeta, d->dcolsum, a.N, a.nacc, grid);
+  reduce_gamma_beta_kernel<<<(a.nacc * a.N + 7) / 8, 256, 0, st>>>(a.part, d->dgamma, d->dbeta, d->dcolsum, a.N, a.nacc, grid);
   ++launches;
   last_launch_count() = launches;
   const cudaError_t err = cudaGetLastError();
