@@ -111,6 +111,9 @@ NA_SHAPES = [
     ("C4 LN2(x1+ff) N384", 256 * 197, 384, None, True, "none", 0.0, torch.bfloat16),
     ("C4 GELU(LN(h1))+up N1536 f32", 256 * 197, 1536, 384, False, "gelu", 0.001, torch.float32),
     ("C3 GELU(LN(h1))+general 512->768", 1024 * 65, 768, 512, False, "gelu", 0.001, torch.bfloat16),
+    ("C3 GELU(LN(h2))+general 768->512", 1024 * 65, 512, 768, False, "gelu", 0.001, torch.bfloat16),
+    ("C2 GELU(LN(h1))+general 48->256 f32", 4096 * 50, 256, 48, False, "gelu", 0.001, torch.float32),
+    ("C2 GELU(LN(h2))+general 256->48 f32", 4096 * 50, 48, 256, False, "gelu", 0.001, torch.float32),
 ]
 
 

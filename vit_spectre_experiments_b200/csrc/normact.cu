@@ -210,21 +210,27 @@ __device__ __forceinline__ void pool_windows(unsigned* tab, int n_out, int n_in)
   }
 }
 // o[0..8) += pool(skip)[j0 .. j0+8)
+// `short_win`: every window has one or two elements (N >= Ns): branch-free, (first + last) / 2
 template <class T>
-__device__ __forceinline__ void skip_general_add(const T* srow, const unsigned* win, int j0, float (&o)[8]) {
+__device__ __forceinline__ void skip_general_add(const T* srow, const unsigned* win, int j0, bool short_win, float (&o)[8]) {
   const uint4 wa = *reinterpret_cast<const uint4*>(win + j0), wb = *reinterpret_cast<const uint4*>(win + j0 + 4);
   const unsigned w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
     const int s = static_cast<int>(w[e] & 0xffffu), n = static_cast<int>(w[e] >> 16);
-    float acc = ld1(srow + s);
-    for (int k = 1; k < n; ++k) acc += ld1(srow + s + k);
-    o[e] = fmaf(acc, rcp_approx(static_cast<float>(n)), o[e]);
+    if (short_win) {
+      o[e] = fmaf(0.5f, ld1(srow + s) + ld1(srow + s + n - 1), o[e]);
+    } else {
+      float acc = ld1(srow + s);
+      for (int k = 1; k < n; ++k) acc += ld1(srow + s + k);
+      o[e] = fmaf(acc, rcp_approx(static_cast<float>(n)), o[e]);
+    }
   }
 }
 // d_skip[c0 .. c0+8) of one row from the row's window-normalised gradients dn[j] = d[j] / len(j) (shared memory)
+// `short_cov`: every skip column feeds one or two outputs (N <= Ns): branch-free
 template <class T>
-__device__ __forceinline__ void skip_general_bwd(T* drow, const float* dn, const unsigned* cov, int c0) {
+__device__ __forceinline__ void skip_general_bwd(T* drow, const float* dn, const unsigned* cov, int c0, bool short_cov) {
   const uint4 wa = *reinterpret_cast<const uint4*>(cov + c0), wb = *reinterpret_cast<const uint4*>(cov + c0 + 4);
   const unsigned w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
   float g[8];
@@ -232,7 +238,12 @@ __device__ __forceinline__ void skip_general_bwd(T* drow, const float* dn, const
   for (int e = 0; e < 8; ++e) {
     const int s = static_cast<int>(w[e] & 0xffffu), n = static_cast<int>(w[e] >> 16);
     float acc = dn[s];
-    for (int k = 1; k < n; ++k) acc += dn[s + k];
+    if (short_cov) {
+      const float b = dn[s + n - 1];
+      acc = n == 2 ? acc + b : acc;
+    } else {
+      for (int k = 1; k < n; ++k) acc += dn[s + k];
+    }
     g[e] = acc;
   }
   st8(drow + c0, g);
@@ -287,7 +298,7 @@ __device__ __forceinline__ void skip_down_bwd(T* drow, int j0, const float (&d)[
 
 // ------------------------------------------------------------------ forward
 template <class T, int VPT, int MODE, int ACT>
-__global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
+__global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(const Args a) {
   extern __shared__ __align__(128) uint8_t ring[];
   __shared__ uint64_t full[kMaxStages];
   __shared__ float red[2][2][8];
@@ -400,7 +411,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_fwd_kernel(const Args a) {
         } else if constexpr (down_k(MODE) > 0) {
           skip_down_add<T, down_k(MODE)>(srow, j0, o);
         } else if constexpr (MODE == kSkipGeneral) {
-          skip_general_add<T>(srow, win, j0, o);
+          skip_general_add<T>(srow, win, j0, a.N >= a.Ns, o);
         }
         if (drop) {
           const unsigned vh = vec_hash(rseed, static_cast<unsigned>(v));
@@ -572,7 +583,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
     if constexpr (MODE == kSkipGeneral) {
       if (wpr == 1) __syncwarp();   // one warp per row: dn is written and read by the same warp
       if (live)
-        for (int u = t; u < (a.Ns >> 3); u += tpr) skip_general_bwd<T>(static_cast<T*>(a.d_skip) + row * a.Ns, dn, cov, u * 8);
+        for (int u = t; u < (a.Ns >> 3); u += tpr) skip_general_bwd<T>(static_cast<T*>(a.d_skip) + row * a.Ns, dn, cov, u * 8, a.N <= a.Ns);
     }
     if (live) {
       const float m1 = s[0] * inv_n, m2 = s[1] * inv_n;
@@ -665,7 +676,14 @@ static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, 
   Shape sh{};
   const int nvec = N / 8;
   if (nvec <= 32) { sh.vpt = 1; sh.tpr = 32; }
-  else { sh.vpt = 2; sh.tpr = ((nvec + 1) / 2 + 31) / 32 * 32; }
+  else {
+    // 2 or 3 vectors per thread: fewest idle lanes first, then the larger count (fewer warps per row: cheaper
+    // row sums, more work per thread between barriers)
+    const int t2 = ((nvec + 1) / 2 + 31) / 32 * 32, t3 = ((nvec + 2) / 3 + 31) / 32 * 32;
+    // (forward only: the backward's shared-memory accumulators scale with rows per CTA and would leave 8 warps per SM)
+    if (!bwd && t3 * 3 <= t2 * 2) { sh.vpt = 3; sh.tpr = t3; }
+    else { sh.vpt = 2; sh.tpr = t2; }
+  }
   // bytes of one row in the ring: forward in0 (+ in1) + skip; backward dout + in0 (+ in1)
   const int row_bytes = bwd ? N * elem * (2 + (has_in1 ? 1 : 0) + (has_dout2 ? 1 : 0))
                             : N * elem * (has_in1 ? 2 : 1) + (has_skip ? Ns * elem : 0);
@@ -676,7 +694,7 @@ static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, 
   // ring depth: whatever keeps three CTAs resident (~74 KB each) next to the backward's accumulators
   size_t fixed = bwd ? static_cast<size_t>(nacc * sh.rpc + 2) * N * sizeof(float) : 0;
   if (general) fixed += bwd ? (static_cast<size_t>(sh.rpc + 1) * N + Ns) * sizeof(float) : N * sizeof(float);
-  const long long room = 74 * 1024 - static_cast<long long>(fixed);
+  const long long room = (sh.vpt == 3 ? 108 : 74) * 1024 - static_cast<long long>(fixed);   // vpt 3: two CTAs per SM
   sh.stages = room > 0 ? static_cast<int>(room / sh.stage_bytes) : 0;
   if (sh.stages < 2) sh.stages = 2;
   if (sh.stages > kMaxStages) sh.stages = kMaxStages;
@@ -721,7 +739,8 @@ static Args to_args(const spectre_norm_act_t& d, bool bwd) {
 static int grid_for(long long rows, const Shape& sh) {
   const long long groups = (rows + sh.rpc - 1) / sh.rpc;
   const int block = sh.tpr * sh.rpc;
-  int per_sm = 768 / block;                        // <= 3 CTAs of 256 threads (80 registers each)
+  // resident threads per SM by registers: 768 (80 registers each); 512 for the 3-vector variants (<= 128 each)
+  int per_sm = (sh.vpt == 3 ? 512 : 768) / block;
   if (per_sm < 1) per_sm = 1;
   if (per_sm > 6) per_sm = 6;
   const int by_smem = static_cast<int>((220 * 1024) / (sh.smem + 1024));
@@ -734,24 +753,29 @@ static int grid_for(long long rows, const Shape& sh) {
 typedef void (*KernelFn)(const Args);
 template <class T, int VPT, int ACT, int... M>
 static void fill_row(KernelFn* fwd, KernelFn* bwd, std::integer_sequence<int, M...>) {
-  ((fwd[M] = norm_act_fwd_kernel<T, VPT, M, ACT>, bwd[M] = norm_act_bwd_kernel<T, VPT, M, ACT>), ...);
+  ((fwd[M] = norm_act_fwd_kernel<T, VPT, M, ACT>), ...);
+  if constexpr (VPT <= 2) ((bwd[M] = norm_act_bwd_kernel<T, VPT, M, ACT>), ...);   // 3 vectors per thread: forward only
 }
 struct KernelTable {
-  KernelFn fwd[2][2][2][kSkipModes], bwd[2][2][2][kSkipModes];
-  KernelTable() {
+  KernelFn fwd[2][3][2][kSkipModes], bwd[2][3][2][kSkipModes];
+  KernelTable() : fwd{}, bwd{} {
     using Seq = std::make_integer_sequence<int, kSkipModes>;
     fill_row<float, 1, 0>(fwd[0][0][0], bwd[0][0][0], Seq{});
     fill_row<float, 1, 1>(fwd[0][0][1], bwd[0][0][1], Seq{});
     fill_row<float, 2, 0>(fwd[0][1][0], bwd[0][1][0], Seq{});
     fill_row<float, 2, 1>(fwd[0][1][1], bwd[0][1][1], Seq{});
+    fill_row<float, 3, 0>(fwd[0][2][0], bwd[0][2][0], Seq{});
+    fill_row<float, 3, 1>(fwd[0][2][1], bwd[0][2][1], Seq{});
     fill_row<__nv_bfloat16, 1, 0>(fwd[1][0][0], bwd[1][0][0], Seq{});
     fill_row<__nv_bfloat16, 1, 1>(fwd[1][0][1], bwd[1][0][1], Seq{});
     fill_row<__nv_bfloat16, 2, 0>(fwd[1][1][0], bwd[1][1][0], Seq{});
     fill_row<__nv_bfloat16, 2, 1>(fwd[1][1][1], bwd[1][1][1], Seq{});
+    fill_row<__nv_bfloat16, 3, 0>(fwd[1][2][0], bwd[1][2][0], Seq{});
+    fill_row<__nv_bfloat16, 3, 1>(fwd[1][2][1], bwd[1][2][1], Seq{});
     for (auto& t : fwd) for (auto& v : t) for (auto& w : v) for (KernelFn f : w)
       cudaFuncSetAttribute(reinterpret_cast<const void*>(f), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     for (auto& t : bwd) for (auto& v : t) for (auto& w : v) for (KernelFn f : w)
-      cudaFuncSetAttribute(reinterpret_cast<const void*>(f), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      if (f) cudaFuncSetAttribute(reinterpret_cast<const void*>(f), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   }
 };
 static const KernelTable& table() {
