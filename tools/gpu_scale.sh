@@ -8,3 +8,8 @@ python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127
 fi
 grep '"metric"' gpurun_out/scale_n$N.json | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['n_gpus'], d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac'])"
 done
+# the DWT config (C3) at the largest N given, for the record
+if [ "${N:-1}" != "1" ]; then
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --config c3 --gpus $N --steps 10 --warmup 3 > gpurun_out/scale_c3_n$N.json 2> gpurun_out/scale_c3_n$N.err; echo "c3 n$N rc=$?"
+grep '"metric"' gpurun_out/scale_c3_n$N.json | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('c3', d['n_gpus'], d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac'])"
+fi
