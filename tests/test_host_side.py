@@ -138,3 +138,34 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src, f
+
+
+@pytest.mark.parametrize("T,E", [(65, 64), (50, 48), (197, 24)])
+def test_fnet_mix_matches_fft2_real(T, E):
+    """``fft_bare`` occupant of the slot (orthogonal_permut.py:23-28): two real GEMMs == Re(fft2) over (T, E),
+    forward and input gradient (float64 so the comparison is at rounding level)."""
+    from vit_spectre_experiments_b200.mixers import FNetMix
+
+    torch.manual_seed(3)
+    m = FNetMix(E, T, 4, E)
+    assert len(m.state_dict()) == 0                       # constant matrices stay out of checkpoints
+    x = torch.randn(3, T, E, dtype=torch.float64, requires_grad=True)
+    y = m(x)
+    ref = torch.fft.fft2(x, dim=(-2, -1)).real
+    assert y.shape == x.shape
+    assert (y - ref).abs().max() <= 1e-9 * ref.abs().max()
+    g = torch.randn_like(y)
+    (dx,) = torch.autograd.grad(y, x, g)
+    (dref,) = torch.autograd.grad(ref, x, g)
+    assert (dx - dref).abs().max() <= 1e-9 * dref.abs().max()
+
+
+def test_fnet_mixer_in_the_model():
+    from vit_spectre_experiments_b200.model import SpectreViT
+
+    torch.manual_seed(0)
+    net = SpectreViT(img_size=32, patch_size=4, in_channels=3, num_classes=10, embed_dim=32, num_encoders=2,
+                     num_heads=4, hidden_dim=48, dropout=0.0, activation="gelu", mixer="fnet")
+    out = net(torch.randn(2, 3, 32, 32))
+    assert out.shape == (2, 10) and torch.isfinite(out).all()
+    out.sum().backward()

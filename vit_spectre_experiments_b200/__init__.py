@@ -8,7 +8,7 @@ Public surface
                                          ``mixer=`` switch at the one line that builds ``mix_layer``
 """
 from .functional import dwt_mix, fft_mix  # noqa: F401
-from .mixers import HaarDWTMix, SpectralFilterMix  # noqa: F401
+from .mixers import FNetMix, HaarDWTMix, SpectralFilterMix  # noqa: F401
 from .model import (  # noqa: F401
     MHPermutMix,
     SpectralPatchEmbed,

@@ -113,3 +113,41 @@ class HaarDWTMix(_Fp32ParamMixin, nn.Module):
 
     def extra_repr(self) -> str:
         return f"embed_dim={self.embed_dim}, grid={self.grid}, has_cls={self.has_cls}"
+
+
+class FNetMix(nn.Module):
+    """``fft_bare`` (FNet): ``Re(fft2(x, dim=(-2, -1)))`` over (tokens, channels), parameter-free
+    (``spectre_vit/repl/orthogonal_permut.py:23-28``; mode name ``spectre.py:31``).
+
+    ``Re(F_T x F_E) = C_T x C_E - S_T x S_E`` with the cosine / sine DFT matrices, i.e. two dense real GEMMs
+    ``x @ [C_E | S_E]`` and ``[C_T | -S_T] @ [xC ; xS]``: GEMM-shaped work, left to the library GEMM (cuBLAS) --
+    no custom kernel, no complex intermediates, and it runs in the activation dtype under autocast.  The
+    matrices are non-persistent buffers: the module adds nothing to ``state_dict()``.
+    """
+
+    def __init__(self, embed_dim: int, token_dim: int, num_heads: int, out_channels: int):
+        super().__init__()
+        if out_channels != embed_dim:
+            raise ValueError("FNetMix keeps the channel count: out_channels must equal embed_dim")
+        self.embed_dim, self.token_dim, self.num_heads = embed_dim, token_dim, num_heads
+
+        def cos_sin(n):
+            k = torch.arange(n, dtype=torch.int64)
+            ang = (2.0 * math.pi / n) * ((k[:, None] * k[None, :]) % n).to(torch.float64)
+            return torch.cos(ang), torch.sin(ang)
+
+        ce, se = cos_sin(embed_dim)
+        ct, st = cos_sin(token_dim)
+        self.register_buffer("dft_e", torch.cat([ce, se], dim=1), persistent=False)     # [E, 2E], float64 master
+        self.register_buffer("dft_t", torch.cat([ct, -st], dim=1), persistent=False)    # [T, 2T]
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.dim() != 3 or x.shape[1] != self.token_dim or x.shape[2] != self.embed_dim:
+            raise ValueError(f"FNetMix expects [B, {self.token_dim}, {self.embed_dim}], got {tuple(x.shape)}")
+        E = self.embed_dim
+        xe = torch.matmul(x, self.dft_e.to(x.dtype))                   # [B, T, 2E] = [x C_E | x S_E]
+        stacked = torch.cat([xe[..., :E], xe[..., E:]], dim=1)         # [B, 2T, E]
+        return torch.matmul(self.dft_t.to(x.dtype), stacked)           # C_T (x C_E) - S_T (x S_E)
+
+    def extra_repr(self) -> str:
+        return f"embed_dim={self.embed_dim}, token_dim={self.token_dim}"

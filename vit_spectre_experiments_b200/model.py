@@ -25,9 +25,9 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .mixers import HaarDWTMix, SpectralFilterMix
+from .mixers import FNetMix, HaarDWTMix, SpectralFilterMix
 
-MIXERS = ("permut", "fft", "dwt")
+MIXERS = ("permut", "fft", "dwt", "fnet")
 
 # SB200_FUSED=0 keeps the stock torch composition of LayerNorm / GELU / pool / add around the mixer and
 # the GEMMs on CUDA too (A/B measurements); default: the fused norm_act kernels (fused.py).
@@ -106,6 +106,8 @@ def build_mixer(mixer: str, d_model: int, seq_length: int, nhead: int, grid=None
         return SpectralFilterMix(d_model, seq_length, nhead, d_model, grid=grid)
     if mixer == "dwt":
         return HaarDWTMix(d_model, seq_length, nhead, d_model, grid=grid)
+    if mixer == "fnet":
+        return FNetMix(d_model, seq_length, nhead, d_model)
     raise ValueError(f"unknown mixer {mixer!r}; choose from {MIXERS}")
 
 
