@@ -3,6 +3,7 @@
 set -u
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
 python bench.py --steps 20 --warmup 5 > gpurun_out/bench_c4.json 2> gpurun_out/bench_c4.err; echo "bench rc=$?"; cat gpurun_out/bench_c4.json
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_c4_reference.json 2>> gpurun_out/bench_c4.err; echo "bench ref rc=$?"; cat gpurun_out/bench_c4_reference.json
 for b in 256 1024; do python bench.py --steps 20 --warmup 5 --batch $b --no-cpu-baseline > gpurun_out/bench_c4_b$b.json 2>> gpurun_out/bench_c4.err; echo "bench$b rc=$?"; cut -c1-200 gpurun_out/bench_c4_b$b.json; done
