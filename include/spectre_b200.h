@@ -125,6 +125,13 @@ int spectre_permut_fwd(const void* x, const long long* perms, const float* signs
 int spectre_permut_bwd(const void* dout, const long long* inv_perms, const float* signs, void* dx,
                        int B, long long F, int heads, int act_dtype, void* stream);
 
+/* Measurement hook (bench.py's per-kernel roofline): the next backward mixer call on this thread records `event`
+ * (a cudaEvent_t) on its stream right after its main kernel, i.e. before the small partial-gradient reduction kernel.
+ * spectre_debug_mark_pending() returns 1 and disarms the hook if no call consumed it (single-slab launches have no
+ * reduction kernel). */
+void spectre_debug_mark_main_kernel_end(void* event);
+int spectre_debug_mark_pending(void);
+
 /* 1 if (H, W) has a compiled FFT-mixer kernel, else 0. */
 int spectre_fftmix_supported(int H, int W);
 

@@ -151,7 +151,7 @@ def norm_act_bench(args, dev, flush):
                 TIMER.reset(); TIMER.enabled = True
                 fn()
                 TIMER.enabled = False
-                (n, ms, _), = TIMER.summary().values()
+                (n, ms, _, _), = TIMER.summary().values()
                 if it >= 3:
                     ts.append(ms)
             ts.sort()

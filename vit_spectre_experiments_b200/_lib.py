@@ -25,6 +25,8 @@ EXPORTED_SYMBOLS = (
     "spectre_norm_act_bwd_workspace_bytes",
     "spectre_permut_fwd",
     "spectre_permut_bwd",
+    "spectre_debug_mark_main_kernel_end",
+    "spectre_debug_mark_pending",
     "spectre_fftmix_supported",
     "spectre_last_launch_count",
     "spectre_last_error",
@@ -64,6 +66,10 @@ def load() -> ctypes.CDLL:
                 "Build it with `python -m vit_spectre_experiments_b200.build` (needs nvcc)."
             )
         lib = ctypes.CDLL(LIB_PATH)
+        lib.spectre_debug_mark_main_kernel_end.argtypes = [_p]
+        lib.spectre_debug_mark_main_kernel_end.restype = None
+        lib.spectre_debug_mark_pending.argtypes = []
+        lib.spectre_debug_mark_pending.restype = _i
         lib.spectre_fftmix_fwd.argtypes = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p]
         lib.spectre_fftmix_fwd.restype = _i
         lib.spectre_fftmix_bwd.argtypes = [_p, _p, _p, _p, _p, _p, _sz, _i, _i, _i, _i, _i, _i, _p]

@@ -81,7 +81,14 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const float4* __re
   }
 }
 
+// measurement hook: an event to record between a backward mixer's main kernel and its partial-gradient reduction
+static thread_local cudaEvent_t g_main_end_event = nullptr;
+
 void launch_reduce_partials(const float* part, float* out, size_t n_floats, int slabs, cudaStream_t stream) {
+  if (g_main_end_event) {
+    cudaEventRecord(g_main_end_event, stream);
+    g_main_end_event = nullptr;
+  }
   const size_t n4 = n_floats / 4;
   const unsigned blocks = static_cast<unsigned>((n4 + 63) / 64);
   reduce_partials_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(part),
@@ -102,6 +109,13 @@ static int check_common(const char* fn, int B, int H, int W, int E, int has_cls,
 using namespace sb200;
 
 extern "C" {
+
+void spectre_debug_mark_main_kernel_end(void* event) { g_main_end_event = static_cast<cudaEvent_t>(event); }
+int spectre_debug_mark_pending(void) {
+  const int pending = g_main_end_event != nullptr;
+  g_main_end_event = nullptr;
+  return pending;
+}
 
 int spectre_fftmix_fwd(const void* x, const float* filt, void* y, int B, int H, int W, int E, int has_cls, int act_dtype,
                        void* stream) {

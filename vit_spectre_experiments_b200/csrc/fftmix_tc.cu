@@ -220,6 +220,8 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
   const int img0 = blockIdx.x / p.nct;
   const int c0 = ct * kTileC;
   const int ntiles = img0 < p.B ? (p.B - img0 + p.img_stride - 1) / p.img_stride : 0;
+  // images are swept from the last to the first: the producer of x (a row kernel sweeping upwards) left its most
+  // recent ~100 MB in L2, and the consumer of y starts at image 0, which this sweep writes last
   const bool half1 = c0 + 64 < p.E;
 
   // ---- one-time setup
@@ -234,7 +236,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     const uint32_t bytes0 = (half1 ? 2u : 1u) * C::HW * 128u;
     for (int it = 0; it < S && it < ntiles; ++it) {
       uint8_t* dst = smem + it * C::kStageBytes;
-      const int b = img0 + it * p.img_stride;
+      const int b = img0 + (ntiles - 1 - it) * p.img_stride;
       mbar_arrive_expect_tx(&full_bar[it], bytes0);
       tma_load_3d(dst, &tmap_x, &full_bar[it], c0, 0, b);
       if (half1) tma_load_3d(dst + C::kHalfStride, &tmap_x, &full_bar[it], c0 + 64, 0, b);
@@ -309,7 +311,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 
     for (int it = 0; it < ntiles; ++it) {
       const uint32_t par = it & 1;
-      const int b = img0 + it * p.img_stride;
+      const int b = img0 + (ntiles - 1 - it) * p.img_stride;
       // ---------------- E1: D1[h][slot,ri] -> A2[kw][h] (bf16 pairs)
       if (stamp) SB200_STAMP(g, it, 0);
       {
@@ -568,7 +570,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
       const uint32_t bytes = (half1 ? 2u : 1u) * C::HW * 128u;
       for (int it = 0; it < ntiles; ++it) {
         const int s = it % S;
-        const int b = img0 + it * p.img_stride;
+        const int b = img0 + (ntiles - 1 - it) * p.img_stride;
         if (it >= S) mbar_wait(&empty_bar[s], ((it / S) - 1) & 1);
         if (lane == 0 && it >= S) {
           SB200_STAMP(3, it, 0);
@@ -770,7 +772,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
     for (int k = 0; k < 24; ++k) mbar_init(&dready_bar[k >> 2][k & 3], 1);
     mbar_fence_init();
     if (ntiles > 0) {   // prologue: first tile's dy and x
-      const int b0 = 2 * pair0;
+      const int b0 = 2 * (pair0 + (ntiles - 1) * p.pair_stride);   // first tile in the (descending) sweep
       const bool two = b0 + 1 < p.B;
       const uint32_t bytes = (two ? 2u : 1u) * C::HW * 128u;
       mbar_arrive_expect_tx(&full_bar[0], bytes);
@@ -866,7 +868,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
 
     for (int it = 0; it < ntiles; ++it) {
       const uint32_t par = it & 1;
-      const int b0 = 2 * (pair0 + it * p.pair_stride);
+      const int b0 = 2 * (pair0 + (ntiles - 1 - it) * p.pair_stride);
       const bool two = b0 + 1 < p.B;
       const bool mvalid = m < 64 || two;
       // ---------------- rows(dy) -> A_dy ; rows(x) -> A_x
@@ -1166,7 +1168,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
       // ========================================================= TMA producer + CLS pass-through
       const int T = C::HW + p.cls;
       for (int it = 0; it < ntiles; ++it) {
-        const int b0 = 2 * (pair0 + it * p.pair_stride);
+        const int b0 = 2 * (pair0 + (ntiles - 1 - it) * p.pair_stride);
         const bool two = b0 + 1 < p.B;
         const uint32_t bytes = (two ? 2u : 1u) * C::HW * 128u;
         if (it > 0) {

@@ -19,18 +19,22 @@ class KernelTimer:
 
     def __init__(self):
         self.enabled = False
-        self.records = {}   # name -> list of (start_event, end_event, meta)
+        self.records = {}   # name -> list of (start_event, end_event, meta, main_kernel_end_event)
 
     def reset(self):
         self.records = {}
 
     def summary(self):
-        """name -> (launches, mean_ms, meta of the last call); synchronises."""
+        """name -> (calls, mean ms of the whole C-ABI call, meta of the last call, mean ms of the call's main
+        kernel alone); synchronises.  The last value differs from the second only for backward mixer calls, which
+        end with a few-microsecond reduction kernel of the per-slab parameter gradients."""
         torch.cuda.synchronize()
         out = {}
         for name, evs in self.records.items():
-            ms = [s.elapsed_time(e) for s, e, _ in evs]
-            out[name] = (len(ms), sum(ms) / max(len(ms), 1), evs[-1][2])
+            ms = [s.elapsed_time(e) for s, e, _, _ in evs]
+            main = [s.elapsed_time(m) for s, _, _, m in evs]
+            n = max(len(ms), 1)
+            out[name] = (len(ms), sum(ms) / n, evs[-1][2], sum(main) / n)
         return out
 
 
@@ -38,20 +42,27 @@ TIMER = KernelTimer()
 
 
 class _timed:
-    def __init__(self, name, meta):
-        self.name, self.meta = name, meta
+    def __init__(self, name, meta, mark_main=False):
+        self.name, self.meta, self.mark_main = name, meta, mark_main
 
     def __enter__(self):
         if TIMER.enabled:
             self.s = torch.cuda.Event(enable_timing=True)
             self.e = torch.cuda.Event(enable_timing=True)
             self.s.record()
+            if self.mark_main:   # the library re-records this event between the main kernel and the reduction
+                self.m = torch.cuda.Event(enable_timing=True)
+                self.m.record()  # creates the underlying cudaEvent_t
+                _lib.load().spectre_debug_mark_main_kernel_end(self.m.cuda_event)
         return self
 
     def __exit__(self, *exc):
         if TIMER.enabled:
             self.e.record()
-            TIMER.records.setdefault(self.name, []).append((self.s, self.e, self.meta))
+            main_end = self.e
+            if self.mark_main and not _lib.load().spectre_debug_mark_pending():
+                main_end = self.m
+            TIMER.records.setdefault(self.name, []).append((self.s, self.e, self.meta, main_end))
         return False
 
 
@@ -110,7 +121,7 @@ def _mix_bwd_raw(kind, dy, x, param, H, W, has_cls):
     with torch.cuda.device(x.device):
         nbytes = ws_fn(B, H, W, E)
         ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
-        with _timed(f"{kind}mix_bwd", (B, H, W, E, x.element_size())):
+        with _timed(f"{kind}mix_bwd", (B, H, W, E, x.element_size()), mark_main=True):
             rc = fn(dy.data_ptr(), x.data_ptr(), param.data_ptr(), dx.data_ptr(), dparam.data_ptr(), ws.data_ptr(),
                     nbytes, B, H, W, E, int(has_cls), _act_code(x, f"{kind}_mix"), _stream_ptr(x.device))
     _lib.check(rc, f"spectre_{kind}mix_bwd")
