@@ -107,6 +107,8 @@ typedef struct spectre_norm_act_t {
   void* workspace; size_t workspace_bytes;
   long long rows; int N; int Ns; int act_dtype; int act /* 0 identity, 1 GELU(erf) */;
   float eps; float drop_p; unsigned long long seed;
+  int reverse /* 0: rows swept first to last; 1: last to first (same result; lets a caller that knows which end of
+                 the operands its producer left hot in L2 start there) */;
 } spectre_norm_act_t;
 
 int spectre_norm_act_fwd(const spectre_norm_act_t* desc, void* stream);

@@ -153,6 +153,29 @@ def test_norm_act_bwd_second_addend_and_colsum(cuda_device):
         assert rel_err(dcol, x.grad.sum(0)) <= 3e-5   # fp32 sums of the unrounded d_in0
 
 
+def test_norm_act_sweep_direction_is_invisible(cuda_device):
+    """``reverse`` only changes the order in which row groups are visited (to start where the producer left L2 hot):
+    per-row results are bit-identical, the column reductions agree to rounding."""
+    from vit_spectre_experiments_b200.fused import na_bwd, na_fwd
+
+    torch.manual_seed(5)
+    rows, N, Ns = 30001, 384, 1536          # ragged last row group
+    for dt in (torch.float32, torch.bfloat16):
+        in0 = torch.randn(rows, N, device=cuda_device).to(dt)
+        skip = torch.randn(rows, Ns, device=cuda_device).to(dt)
+        gamma, beta = 1 + 0.2 * torch.randn(N, device=cuda_device), 0.1 * torch.randn(N, device=cuda_device)
+        dout = torch.randn(rows, N, device=cuda_device).to(dt)
+        kw = dict(act=1, drop_p=0.05, seed=123)
+        fa, fb = na_fwd(in0, gamma, beta, skip=skip, **kw), na_fwd(in0, gamma, beta, skip=skip, reverse=True, **kw)
+        for u, v in zip(fa, fb):
+            assert torch.equal(u, v)
+        ba = na_bwd(dout, in0, gamma, beta, fa[1], fa[2], skip_shape=(rows, Ns), colsum=True, **kw)
+        bb = na_bwd(dout, in0, gamma, beta, fa[1], fa[2], skip_shape=(rows, Ns), colsum=True, reverse=True, **kw)
+        assert torch.equal(ba[0], bb[0]) and torch.equal(ba[1], bb[1])
+        for u, v in zip(ba[2:], bb[2:]):
+            assert rel_err(u, v) <= 1e-5
+
+
 @pytest.mark.parametrize("mixer,grid", [("fft", (8, 8)), ("dwt", (8, 8)), ("permut", None)])
 @pytest.mark.parametrize("autocast", [False, True])
 def test_encoder_layer_fused_matches_torch(cuda_device, autocast, mixer, grid):

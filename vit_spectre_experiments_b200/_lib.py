@@ -43,7 +43,7 @@ class NormActDesc(ctypes.Structure):
         ("dgamma", ctypes.c_void_p), ("dbeta", ctypes.c_void_p), ("dcolsum", ctypes.c_void_p), ("workspace", ctypes.c_void_p),
         ("workspace_bytes", ctypes.c_size_t), ("rows", ctypes.c_longlong), ("N", ctypes.c_int), ("Ns", ctypes.c_int),
         ("act_dtype", ctypes.c_int), ("act", ctypes.c_int), ("eps", ctypes.c_float), ("drop_p", ctypes.c_float),
-        ("seed", ctypes.c_ulonglong),
+        ("seed", ctypes.c_ulonglong), ("reverse", ctypes.c_int),
     ]
 
 

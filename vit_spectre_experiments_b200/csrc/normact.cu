@@ -50,6 +50,7 @@ struct Args {
   int tpr; int rpc;                                                 // threads per row, rows per CTA
   int stages; int stage_bytes;                                      // shared-memory ring of input row groups
   float eps; float drop_p; unsigned seed_lo; unsigned seed_hi;
+  int reverse;   // sweep the row groups from the last to the first (the caller knows where the producer left L2 hot)
 };
 
 // ------------------------------------------------------------------ typed vector I/O
@@ -311,13 +312,17 @@ __global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(con
   const float keep_scale = drop ? 1.0f / (1.0f - a.drop_p) : 1.0f;
   const long long groups = (a.rows + a.rpc - 1) / a.rpc;
   const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  auto group_of = [&](int it) {   // row group of iteration it: ascending, or descending from the last group
+    const long long g = blockIdx.x + static_cast<long long>(it) * gridDim.x;
+    return a.reverse ? groups - 1 - g : g;
+  };
   const int off_in1 = a.rpc * a.N * static_cast<int>(sizeof(T));
   const int off_skip = off_in1 * (a.in1 ? 2 : 1);
   unsigned* win = reinterpret_cast<unsigned*>(ring + S * a.stage_bytes);   // general widths: pooling windows [N]
   if constexpr (MODE == kSkipGeneral) pool_windows(win, a.N, a.Ns);
 
   auto issue = [&](int it, int stg) {   // one thread: the group's rows are contiguous in every operand
-    const long long row0 = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc;
+    const long long row0 = group_of(it) * a.rpc;
     const long long left = a.rows - row0;
     const uint32_t nr = static_cast<uint32_t>(left < a.rpc ? left : a.rpc);
     uint8_t* st = ring + stg * a.stage_bytes;
@@ -340,7 +345,7 @@ __global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(con
   for (int it = 0; it < n_it; ++it) {
     if (threadIdx.x == 0 && it + S - 1 < n_it) issue(it + S - 1, stg == 0 ? S - 1 : stg - 1);   // the stage freed by it-1
     ptx::mbar_wait(&full[stg], phase);
-    const long long row = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc + rg;
+    const long long row = group_of(it) * a.rpc + rg;
     const bool live = row < a.rows;
     const uint8_t* st = ring + stg * a.stage_bytes;
     const T* r0 = reinterpret_cast<const T*>(st) + rg * a.N;
@@ -453,11 +458,15 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   const float keep_scale = drop ? 1.0f / (1.0f - a.drop_p) : 1.0f;
   const long long groups = (a.rows + a.rpc - 1) / a.rpc;
   const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  auto group_of = [&](int it) {
+    const long long g = blockIdx.x + static_cast<long long>(it) * gridDim.x;
+    return a.reverse ? groups - 1 - g : g;
+  };
   const int off_in0 = a.rpc * a.N * static_cast<int>(sizeof(T)), off_in1 = 2 * off_in0;
   const int off_d2 = off_in0 * (a.in1 ? 3 : 2);
 
   auto issue = [&](int it, int stg) {   // dout, in0 (, in1) of one row group: contiguous, one bulk copy each
-    const long long row0 = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc;
+    const long long row0 = group_of(it) * a.rpc;
     const long long left = a.rows - row0;
     const uint32_t nr = static_cast<uint32_t>(left < a.rpc ? left : a.rpc);
     uint8_t* st = ring + stg * a.stage_bytes;
@@ -492,18 +501,18 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   // row statistics of the first row (prefetched one iteration ahead afterwards)
   float mean_n = 0.f, rstd_n = 0.f;
   {
-    const long long row = static_cast<long long>(blockIdx.x) * a.rpc + rg;
+    const long long row = group_of(0) * a.rpc + rg;
     if (n_it > 0 && row < a.rows) { mean_n = a.mean[row]; rstd_n = a.rstd[row]; }
   }
   int stg = 0;
   uint32_t phase = 0;
   for (int it = 0; it < n_it; ++it) {
     if (threadIdx.x == 0 && it + S - 1 < n_it) issue(it + S - 1, stg == 0 ? S - 1 : stg - 1);
-    const long long row = (blockIdx.x + static_cast<long long>(it) * gridDim.x) * a.rpc + rg;
+    const long long row = group_of(it) * a.rpc + rg;
     const bool live = row < a.rows;
     const float mean = mean_n, rstd = rstd_n;
     {
-      const long long rown = row + static_cast<long long>(gridDim.x) * a.rpc;
+      const long long rown = group_of(it + 1) * a.rpc + rg;
       if (it + 1 < n_it && rown < a.rows) { mean_n = a.mean[rown]; rstd_n = a.rstd[rown]; }
     }
     ptx::mbar_wait(&full[stg], phase);
@@ -733,6 +742,7 @@ static Args to_args(const spectre_norm_act_t& d, bool bwd) {
   a.rows = d.rows; a.N = d.N; a.Ns = has_skip ? d.Ns : d.N; a.act = d.act; a.eps = d.eps; a.drop_p = d.drop_p;
   a.seed_lo = static_cast<unsigned>(d.seed); a.seed_hi = static_cast<unsigned>(d.seed >> 32);
   a.skip_mode = pick_skip(a.N, a.Ns, has_skip);
+  a.reverse = d.reverse ? 1 : 0;
   return a;
 }
 

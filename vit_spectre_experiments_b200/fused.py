@@ -37,7 +37,7 @@ def _ptr(t):
 
 
 # ------------------------------------------------------------------ raw (non-autograd) kernel calls
-def na_fwd(in0, gamma, beta, in1=None, skip=None, eps=1e-5, act=0, drop_p=0.0, seed=0):
+def na_fwd(in0, gamma, beta, in1=None, skip=None, eps=1e-5, act=0, drop_p=0.0, seed=0, reverse=False):
     """One forward tail.  Returns ``(out, mean, rstd)``; operands must already share in0's dtype."""
     lib = _lib.load()
     if not in0.is_cuda:
@@ -54,6 +54,7 @@ def na_fwd(in0, gamma, beta, in1=None, skip=None, eps=1e-5, act=0, drop_p=0.0, s
     d.out, d.mean, d.rstd = _ptr(out), _ptr(mean), _ptr(rstd)
     d.rows, d.N, d.Ns = rows, N, (skip.shape[-1] if skip is not None else N)
     d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
+    d.reverse = int(bool(reverse))
     with torch.cuda.device(in0.device):
         with _timed("norm_act_fwd", (rows, N, in0.element_size())):
             rc = lib.spectre_norm_act_fwd(ctypes.byref(d), _stream_ptr(in0.device))
@@ -63,7 +64,7 @@ def na_fwd(in0, gamma, beta, in1=None, skip=None, eps=1e-5, act=0, drop_p=0.0, s
 
 
 def na_bwd(dout, in0, gamma, beta, mean, rstd, in1=None, skip_shape=None, eps=1e-5, act=0, drop_p=0.0, seed=0,
-           dout2=None, colsum=False):
+           dout2=None, colsum=False, reverse=False):
     """One backward tail.  Returns ``(d_in0, d_skip | None, dgamma, dbeta, dcolsum | None)``; ``d_in0`` is also
     the gradient of ``in1``; ``dcolsum`` = column sums of ``d_in0`` (fp32)."""
     lib = _lib.load()
@@ -80,6 +81,7 @@ def na_bwd(dout, in0, gamma, beta, mean, rstd, in1=None, skip_shape=None, eps=1e
     d.d_in0, d.d_skip, d.dgamma, d.dbeta, d.dcolsum = _ptr(d_in0), _ptr(d_skip), _ptr(dgamma), _ptr(dbeta), _ptr(dcol)
     d.rows, d.N, d.Ns = rows, N, (skip_shape[-1] if skip_shape is not None else N)
     d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
+    d.reverse = int(bool(reverse))
     with torch.cuda.device(dev):
         nws = lib.spectre_norm_act_bwd_workspace_bytes(rows, N)
         ws = torch.empty(max(nws, 16), dtype=torch.uint8, device=dev)
