@@ -205,6 +205,46 @@ def test_encoder_layer_fused_matches_torch(cuda_device, autocast, mixer, grid):
         assert rel_err(pa[k].grad, pb[k].grad) <= (5e-2 if autocast else 1e-4), k
 
 
+@pytest.mark.parametrize("autocast", [False, True])
+def test_stacked_layers_hand_the_gradient_over_in_two_parts(cuda_device, autocast):
+    """SpectreEncoder chains the one-node layers through (y, y_twin): the two addends of a layer's input gradient
+    travel separately and are summed inside the LN2 backward of the layer below.  Same loss and gradients as
+    calling the layers one by one (where each backward adds the parts itself)."""
+    from vit_spectre_experiments_b200 import SpectreEncoder, SpectreEncoderLayer
+
+    torch.manual_seed(11)
+    layer = SpectreEncoderLayer(seq_length=65, d_model=128, nhead=4, dim_feedforward=256, dropout=0.0,
+                                activation="gelu", mixer="fft", grid=(8, 8), fused=True)
+    enc = SpectreEncoder(layer, 3).to(cuda_device)
+    with torch.no_grad():
+        for p in enc.parameters():
+            p.add_(0.05 * torch.randn_like(p))
+    x = torch.randn(8, 65, 128, device=cuda_device)
+    w = torch.randn(8, 65, 128, device=cuda_device)
+
+    def run(chained):
+        xa = x.clone().requires_grad_(True)
+        enc.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            if chained:
+                y = enc(xa)
+            else:
+                out = xa
+                for l in enc.layers:
+                    out = l.forward_fused(out)
+                y = out.to(xa.dtype) + xa
+        (y.float() * w).sum().backward()
+        return y.detach(), xa.grad.clone(), [p.grad.clone() for p in enc.parameters()]
+
+    ya, ga, pa = run(True)
+    yb, gb, pb = run(False)
+    tol = 2e-2 if autocast else 2e-5
+    assert rel_err(ya, yb) == 0.0
+    assert rel_err(ga, gb) <= tol
+    for u, v in zip(pa, pb):
+        assert rel_err(u, v) <= tol
+
+
 def test_host_batch_prefetcher_feeds_the_same_batches(cuda_device):
     """train.HostBatchPrefetcher (bench.py's end-to-end feed): double-buffered pinned-host -> device copies on a side
     stream deliver exactly the staged batches, in order."""

@@ -146,7 +146,7 @@ class SpectreEncoderLayer(nn.Module):
         x = self.norm1(self.mix_layer(x)) + x
         return self.norm2(x + self._ff_block(x))
 
-    def forward_fused(self, x: torch.Tensor) -> torch.Tensor:
+    def forward_fused(self, x: torch.Tensor, x_twin=None, return_twin: bool = False):
         """Same arithmetic through the fused kernels.  Under bf16 autocast the residual stream is bf16 from
         end to end (one cast at the encoder entry; every kernel reads and writes bf16, statistics fp32);
         otherwise everything stays float32.  Returns the layer output in the stream dtype.
@@ -168,14 +168,15 @@ class SpectreEncoderLayer(nn.Module):
         if isinstance(mix, (SpectralFilterMix, HaarDWTMix)) and x.dim() == 3:
             kind, param = ("fft", mix.filter) if isinstance(mix, SpectralFilterMix) else ("dwt", mix.weight)
             return encoder_layer(x, kind, param, mix.grid, mix.has_cls, self.norm1, lin1, ln1, lin3, ln3, self.norm2,
-                                 p1, p2, s1, s2)
+                                 p1, p2, s1, s2, x_twin=x_twin, return_twin=return_twin)
         m = mix(x)
         x1 = norm_act(m, self.norm1.weight, self.norm1.bias, skip=x, eps=self.norm1.eps)
         h1 = F.linear(x1, lin1.weight, lin1.bias)
         a1 = norm_act(h1, ln1.weight, ln1.bias, skip=x1, eps=ln1.eps, act="gelu", drop_p=p1, seed=s1)
         h2 = F.linear(a1, lin3.weight, lin3.bias)
         ff = norm_act(h2, ln3.weight, ln3.bias, skip=a1, eps=ln3.eps, act="gelu", drop_p=p2, seed=s2)
-        return norm_act(x1, self.norm2.weight, self.norm2.bias, in1=ff, eps=self.norm2.eps)
+        out = norm_act(x1, self.norm2.weight, self.norm2.bias, in1=ff, eps=self.norm2.eps)
+        return (out, None) if return_twin else out
 
 
 class SpectreEncoder(nn.Module):
@@ -191,8 +192,9 @@ class SpectreEncoder(nn.Module):
     def forward(self, src: torch.Tensor) -> torch.Tensor:
         out = src
         if all(isinstance(l, SpectreEncoderLayer) and l.use_fused(src) for l in self.layers):
+            twin = None                 # second addend of the gradient between stacked one-node layers (fused.py)
             for layer in self.layers:   # bf16 stream under bf16 autocast, fp32 otherwise
-                out = layer.forward_fused(out)
+                out, twin = layer.forward_fused(out, twin, return_twin=True)
             out = out.to(src.dtype)
         else:
             for layer in self.layers:
