@@ -13,18 +13,21 @@
 // Every activation tensor of a call has ONE element type T (float32, or bfloat16 for the bf16 training
 // stream); statistics, gamma/beta and all arithmetic are fp32.
 //
-// Mapping: a row is owned by TPR threads (a whole number of warps); a thread owns VPT vectors of 8
+// Mapping: a row is owned by TPR threads (a whole number of warps); a thread owns VPT (1-3) vectors of 8
 // consecutive columns (16-byte bf16 / 2x16-byte fp32 accesses, coalesced).  A CTA of up to 256 threads
-// carries RPC = 256 / TPR rows at a time (narrow rows: one warp per row, no barrier at all) and strides
-// over the rows, so the per-column gamma/beta gradient accumulators stay in registers for the whole
-// kernel and are folded across the CTA's rows in shared memory before ONE partial per CTA is written.
+// carries RPC = 256 / TPR rows at a time (narrow rows: one warp per row, no barrier inside a row) and strides
+// over the row groups (ascending, or descending with `reverse`).  LayerNorm statistics take one pass: sum and
+// sum of squares about a pivot from the row itself.  The backward keeps the per-column gamma / beta /
+// column-sum accumulators of every row group in shared memory (a thread only touches its own columns) and
+// folds them in a fixed order into ONE partial per CTA, reduced by reduce_gamma_beta_kernel: deterministic.
 // Loads are decoupled from the math: the rows of a group are contiguous in every operand, so ONE thread
 // issues one bulk async copy (cp.async.bulk, the 1-D TMA path) per operand per group into a 2-4 stage
 // shared-memory ring, completion on an mbarrier -- tens of KB in flight per SM at any time without
 // holding registers for them.  Results go straight from registers to HBM with 16-byte stores.
 // The kernels are instruction-bound next to the GELU (erf) and the dropout mask, hence: erf by the
 // Abramowitz-Stegun 7.1.26 rational (|err| < 2e-7, one exp shared with the Gaussian of the derivative),
-// a 32-bit counter hash per element, pooling ratios resolved at compile time.
+// one odd multiply of a per-vector hash per element for the mask, pooling ratios resolved at compile time
+// (general widths: window tables built once per CTA in shared memory, transpose fused into the backward).
 #include <cstdarg>
 #include <utility>
 
