@@ -63,16 +63,18 @@ int spectre_fftmix_bwd(const void* dy, const void* x, const float* filt,
                        int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);
 size_t spectre_fftmix_bwd_workspace_bytes(int B, int H, int W, int E);
 
-/* Haar DWT mixer forward (single-level orthonormal 2-D Haar over the token grid, even H, W;
+/* Haar DWT mixer forward (single-level orthonormal 2-D Haar over the token grid;
  * convention of DWTForward(wave="haar", mode="zero") at spectre_vit/repl/dwt_experiments.py:9,56;
  * mode names dwt_token/dwt_embed at spectre.py:33-34):
  *   y[:,1:] = IDWT( w * DWT(x[:,1:] as [B,H,W,E]) )
- * w: float32 [4, H/2, W/2, E], sub-band order (LL, W-low/H-high, W-high/H-low, HH). */
+ * Odd H or W follow mode="zero": a row / column of zeros is appended before the transform and the result is
+ * cropped back to H x W.  With h2 = ceil(H/2), w2 = ceil(W/2):
+ * w: float32 [4, h2, w2, E], sub-band order (LL, W-low/H-high, W-high/H-low, HH). */
 int spectre_dwtmix_fwd(const void* x, const float* w, void* y,
                        int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);
 
 /* Haar DWT mixer backward (row A6): dx = IDWT(w * DWT(dy)); dw = sum_b DWT(x_b) * DWT(dy_b).
- * dw: float32 [4, H/2, W/2, E], fully overwritten. */
+ * dw: float32 [4, ceil(H/2), ceil(W/2), E], fully overwritten. */
 int spectre_dwtmix_bwd(const void* dy, const void* x, const float* w,
                        void* dx, float* dw, void* workspace, size_t workspace_bytes,
                        int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);

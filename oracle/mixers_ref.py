@@ -168,20 +168,31 @@ def ihaar2d(s4: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def _pad_even(g: torch.Tensor) -> torch.Tensor:
+    """``mode="zero"`` for a length-2 filter: an odd axis gets one zero appended at its end
+    (pytorch_wavelets pads ``p = 2*ceil(N/2) - N`` samples, ``p // 2`` in front and the rest behind)."""
+    B, H, W, E = g.shape
+    if H % 2 == 0 and W % 2 == 0:
+        return g
+    out = g.new_zeros(B, H + H % 2, W + W % 2, E)
+    out[:, :H, :W] = g
+    return out
+
+
 def dwt_mix_ref(x: torch.Tensor, w: torch.Tensor, H: int, W: int) -> torch.Tensor:
-    """y = cat(cls, IDWT(w * DWT(grid))).  w real ``[4, H/2, W/2, E]``."""
+    """y = cat(cls, crop(IDWT(w * DWT(pad(grid))))).  w real ``[4, ceil(H/2), ceil(W/2), E]``."""
     B, T, E = x.shape
-    assert T == 1 + H * W and H % 2 == 0 and W % 2 == 0
-    y = ihaar2d(haar2d(x[:, 1:].reshape(B, H, W, E)) * w)
+    assert T == 1 + H * W
+    y = ihaar2d(haar2d(_pad_even(x[:, 1:].reshape(B, H, W, E))) * w)[:, :H, :W]
     return torch.cat([x[:, :1], y.reshape(B, H * W, E)], dim=1)
 
 
 def dwt_mix_bwd_ref(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, H: int, W: int):
     """Closed-form backward (row A6): dx = IDWT(w * DWT(dy)); dw = sum_b DWT(x) * DWT(dy)."""
     B, T, E = x.shape
-    DY = haar2d(dy[:, 1:].reshape(B, H, W, E))
-    X = haar2d(x[:, 1:].reshape(B, H, W, E))
-    dxg = ihaar2d(DY * w)
+    DY = haar2d(_pad_even(dy[:, 1:].reshape(B, H, W, E)))
+    X = haar2d(_pad_even(x[:, 1:].reshape(B, H, W, E)))
+    dxg = ihaar2d(DY * w)[:, :H, :W]       # crop^T = pad, and the block transform is orthogonal and symmetric
     dx = torch.cat([dy[:, :1], dxg.reshape(B, H * W, E)], dim=1)
     return dx, (X * DY).sum(0)
 
@@ -239,8 +250,8 @@ class OracleDWTMix(nn.Module):
             grid = (s, s)
         self.grid = tuple(grid)
         H, W = self.grid
-        assert H * W + 1 == token_dim and H % 2 == 0 and W % 2 == 0
-        self.weight = nn.Parameter(1.0 + 0.02 * torch.randn(4, H // 2, W // 2, embed_dim))
+        assert H * W + 1 == token_dim
+        self.weight = nn.Parameter(1.0 + 0.02 * torch.randn(4, (H + 1) // 2, (W + 1) // 2, embed_dim))
 
     def forward(self, x):
         H, W = self.grid

@@ -30,7 +30,7 @@ def make(B, H, W, E, dtype, has_cls, seed, kind):
     if kind == "fft":
         p = torch.randn(H, W // 2 + 1, E, 2, generator=g)     # O(1) complex filter, non-Hermitian
     else:
-        p = 1.0 + 0.5 * torch.randn(4, H // 2, W // 2, E, generator=g)
+        p = 1.0 + 0.5 * torch.randn(4, (H + 1) // 2, (W + 1) // 2, E, generator=g)
     return x, dy, p
 
 
@@ -92,6 +92,10 @@ DWT_CASES = [
     (5, 4, 6, 16, torch.float32),            # non-square grid
     (1, 2, 2, 8, torch.bfloat16),
     (700, 8, 8, 64, torch.bfloat16),         # more images than y-slabs
+    (9, 7, 7, 48, torch.float32),            # odd grid: mode="zero" padding (C2-shaped)
+    (6, 7, 7, 48, torch.bfloat16),
+    (4, 5, 8, 16, torch.float32),            # odd x even
+    (33, 13, 3, 8, torch.bfloat16),
 ]
 
 
@@ -165,7 +169,7 @@ def test_errors_are_loud(cuda_device):
         fft_mix(torch.randn(2, 65, 8, device=cuda_device).half(), torch.randn(8, 5, 8, 2, device=cuda_device), (8, 8))
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         fft_mix(torch.randn(2, 65, 8), torch.randn(8, 5, 8, 2), (8, 8))
-    with pytest.raises(RuntimeError, match="even"):
+    with pytest.raises(RuntimeError, match="weight"):   # 7x7 pads to 8x8: the sub-band weights are [4, 4, 4, E]
         dwt_mix(torch.randn(2, 50, 8, device=cuda_device), torch.randn(4, 3, 3, 8, device=cuda_device), (7, 7))
 
 

@@ -72,7 +72,7 @@ def test_library_exports_every_declared_symbol():
     assert lib.spectre_fftmix_fwd(p, p, p, 1, 8, 8, 7, 1, 0, None) == -2      # odd E
     assert lib.spectre_fftmix_fwd(p, p, p, 1, 8, 8, 8, 1, 5, None) == -4      # dtype
     assert lib.spectre_fftmix_fwd(p + 4, p, p, 1, 8, 8, 8, 1, 0, None) == -5  # alignment
-    assert lib.spectre_dwtmix_fwd(p, p, p, 1, 7, 7, 8, 1, 0, None) == -2      # odd grid for Haar
+    assert lib.spectre_dwtmix_fwd(p, p, p, 1, 7, 7, 7, 1, 0, None) == -2      # odd E (odd grids are zero-padded)
 
 
 def test_model_mirror_matches_reference_golden():
@@ -112,8 +112,7 @@ def test_mixer_module_contract():
     assert m.filter.dtype == torch.float32          # learned spectral parameters stay fp32
     d = HaarDWTMix(512, 65, 16, 512)
     assert tuple(d.weight.shape) == (4, 4, 4, 512) and list(d.state_dict()) == ["weight"]
-    with pytest.raises(ValueError):
-        HaarDWTMix(48, 50, 8, 48)                   # 7x7 grid is odd
+    assert tuple(HaarDWTMix(48, 50, 8, 48).weight.shape) == (4, 4, 4, 48)   # 7x7 grid: zero-padded to 8x8
     with pytest.raises(ValueError):
         SpectralFilterMix(48, 51, 8, 48)            # 50 tokens is not a square grid + CLS
     vit = SpectreViT(img_size=32, patch_size=4, num_classes=100, embed_dim=64, num_encoders=3, num_heads=4,

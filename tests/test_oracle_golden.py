@@ -113,3 +113,25 @@ def test_closed_form_backward_equals_autograd():
         y.backward(dy)
         dx, df = O.fft_mix_bwd_ref(dy, x.detach(), f.detach(), H, W)
         assert (dx - x.grad).abs().max() < 1e-12 and (df - f.grad).abs().max() < 1e-12
+
+
+@pytest.mark.parametrize("H,W", [(7, 7), (5, 8), (13, 3)])
+def test_oracle_dwt_odd_grid_zero_mode(H, W):
+    """Odd grids under ``mode="zero"`` (dwt_experiments.py:56): pad one zero row / column, transform, crop.
+    Unit weights reconstruct the input; the closed-form backward equals autograd of the forward."""
+    import torch
+
+    from oracle import mixers_ref as O
+
+    torch.manual_seed(4)
+    B, E = 3, 8
+    x = torch.randn(B, 1 + H * W, E, dtype=torch.float64, requires_grad=True)
+    h2, w2 = (H + 1) // 2, (W + 1) // 2
+    ones = torch.ones(4, h2, w2, E, dtype=torch.float64)
+    assert (O.dwt_mix_ref(x, ones, H, W) - x).abs().max() < 1e-12
+    w = (1 + 0.3 * torch.randn(4, h2, w2, E, dtype=torch.float64)).requires_grad_(True)
+    dy = torch.randn(B, 1 + H * W, E, dtype=torch.float64)
+    y = O.dwt_mix_ref(x, w, H, W)
+    gx, gw = torch.autograd.grad(y, (x, w), dy)
+    dx, dw = O.dwt_mix_bwd_ref(dy, x.detach(), w.detach(), H, W)
+    assert (dx - gx).abs().max() < 1e-12 and (dw - gw).abs().max() < 1e-12

@@ -152,7 +152,6 @@ int spectre_dwtmix_fwd(const void* x, const float* w, void* y, int B, int H, int
                        void* stream) {
   if (!x || !w || !y) return fail(SPECTRE_E_NULL, "spectre_dwtmix_fwd: null pointer");
   if (int rc = check_common("spectre_dwtmix_fwd", B, H, W, E, has_cls, act_dtype)) return rc;
-  if ((H & 1) || (W & 1)) return fail(SPECTRE_E_SHAPE, "spectre_dwtmix_fwd: Haar needs even H, W (got %dx%d)", H, W);
   if (!aligned16(x) || !aligned16(w) || !aligned16(y))
     return fail(SPECTRE_E_ALIGN, "spectre_dwtmix_fwd: pointers must be 16-byte aligned");
   const int rc = dwtmix_dispatch(false, x, nullptr, w, y, nullptr, nullptr, 0, B, H, W, E, has_cls, act_dtype,
@@ -165,7 +164,6 @@ int spectre_dwtmix_bwd(const void* dy, const void* x, const float* w, void* dx, 
                        size_t workspace_bytes, int B, int H, int W, int E, int has_cls, int act_dtype, void* stream) {
   if (!dy || !x || !w || !dx || !dw) return fail(SPECTRE_E_NULL, "spectre_dwtmix_bwd: null pointer");
   if (int rc = check_common("spectre_dwtmix_bwd", B, H, W, E, has_cls, act_dtype)) return rc;
-  if ((H & 1) || (W & 1)) return fail(SPECTRE_E_SHAPE, "spectre_dwtmix_bwd: Haar needs even H, W (got %dx%d)", H, W);
   if (!aligned16(dy) || !aligned16(x) || !aligned16(w) || !aligned16(dx) || !aligned16(dw) || !aligned16(workspace))
     return fail(SPECTRE_E_ALIGN, "spectre_dwtmix_bwd: pointers must be 16-byte aligned");
   const int rc = dwtmix_dispatch(true, dy, x, w, dx, dw, workspace, workspace ? workspace_bytes : 0, B, H, W, E, has_cls,
@@ -175,7 +173,7 @@ int spectre_dwtmix_bwd(const void* dy, const void* x, const float* w, void* dx, 
 }
 
 size_t spectre_dwtmix_bwd_workspace_bytes(int B, int H, int W, int E) {
-  if (B < 1 || E < 2 || H < 2 || W < 2 || (H & 1) || (W & 1)) return 0;
+  if (B < 1 || E < 2 || H < 1 || W < 1) return 0;
   return dwtmix_bwd_workspace(B, H, W, E);
 }
 

@@ -96,7 +96,7 @@ def _mix_fwd_raw(kind, x, param, H, W, has_cls):
     _check_tokens(x, H, W, has_cls, what)
     code = _act_code(x, what)
     E = x.shape[2]
-    want = (H, W // 2 + 1, E, 2) if kind == "fft" else (4, H // 2, W // 2, E)
+    want = (H, W // 2 + 1, E, 2) if kind == "fft" else (4, (H + 1) // 2, (W + 1) // 2, E)
     if param.dtype != torch.float32 or tuple(param.shape) != want:
         name = "filter" if kind == "fft" else "weight"
         raise RuntimeError(f"{what}: {name} must be float32 {list(want)}, got {param.dtype} {tuple(param.shape)}")

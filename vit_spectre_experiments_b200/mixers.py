@@ -88,7 +88,8 @@ class SpectralFilterMix(_Fp32ParamMixin, nn.Module):
 class HaarDWTMix(_Fp32ParamMixin, nn.Module):
     """Single-level 2-D Haar DWT over the patch grid -> learned real sub-band weights -> IDWT.
 
-    Parameter ``weight``: float32 ``[4, H/2, W/2, E]`` ordered (LL, W-low/H-high, W-high/H-low, HH).
+    Parameter ``weight``: float32 ``[4, ceil(H/2), ceil(W/2), E]`` ordered (LL, W-low/H-high, W-high/H-low, HH).
+    Odd grids follow ``mode="zero"`` (dwt_experiments.py:56): zero row / column appended, result cropped.
     """
 
     _fp32_param = "weight"
@@ -104,9 +105,7 @@ class HaarDWTMix(_Fp32ParamMixin, nn.Module):
         self.has_cls = bool(has_cls)
         self.grid = _resolve_grid(token_dim, grid, self.has_cls)
         H, W = self.grid
-        if H % 2 or W % 2:
-            raise ValueError(f"Haar DWT needs an even grid, got {H}x{W}")
-        self.weight = nn.Parameter(1.0 + init_std * torch.randn(4, H // 2, W // 2, embed_dim))
+        self.weight = nn.Parameter(1.0 + init_std * torch.randn(4, (H + 1) // 2, (W + 1) // 2, embed_dim))
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return dwt_mix(self._activation(x), self.weight, self.grid, self.has_cls)
