@@ -241,7 +241,8 @@ def fft_mix(x: torch.Tensor, filt: torch.Tensor, grid, has_cls: bool = True) -> 
 def dwt_mix(x: torch.Tensor, weight: torch.Tensor, grid, has_cls: bool = True) -> torch.Tensor:
     """``cat(cls, IDWT_haar(weight * DWT_haar(x_grid)))`` in one fused CUDA pass.
 
-    weight float32 ``[4, H/2, W/2, E]`` ordered (LL, W-low/H-high, W-high/H-low, HH).
+    weight float32 ``[4, ceil(H/2), ceil(W/2), E]`` ordered (LL, W-low/H-high, W-high/H-low, HH); odd grids are
+    zero-padded (``mode="zero"``) and cropped.
     """
     H, W = grid
     return _Mix.apply(x, weight, "dwt", int(H), int(W), bool(has_cls))
