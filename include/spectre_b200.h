@@ -117,6 +117,20 @@ int spectre_norm_act_fwd(const spectre_norm_act_t* desc, void* stream);
 int spectre_norm_act_bwd(const spectre_norm_act_t* desc, void* stream);
 size_t spectre_norm_act_bwd_workspace_bytes(long long rows, int N);
 
+/* Multi-level Haar DWT mixer (J = levels, the reference call site uses J=3: dwt_experiments.py:56; H and W multiples
+ * of 2^levels, H*W <= 256, E a multiple of 4):  y[:,1:] = T^-1( w * T(x[:,1:]) ), T = J-level orthonormal 2-D Haar.
+ * Coefficients are addressed IN PLACE on the token lattice: level l works on the 2x2 blocks (a b / c d, b next along W,
+ * c next along H) of the points whose coordinates are multiples of 2^(l-1) and leaves LL at a, low-W/high-H at c,
+ * high-W/low-H at b, HH at d; the next level recurses on the LL points.  w and dw: float32 [H, W, E] in that layout
+ * (for levels = 1: w[0::2,0::2] = LL, w[1::2,0::2], w[0::2,1::2], w[1::2,1::2] = the three detail bands of
+ * spectre_dwtmix_fwd in its order).  Backward: dx = T^-1(w * T dy), dw = sum_b T(x_b) * T(dy_b), fully overwritten. */
+int spectre_dwtmix_ml_fwd(const void* x, const float* w, void* y,
+                          int B, int H, int W, int E, int has_cls, int levels, int act_dtype, void* stream);
+int spectre_dwtmix_ml_bwd(const void* dy, const void* x, const float* w,
+                          void* dx, float* dw, void* workspace, size_t workspace_bytes,
+                          int B, int H, int W, int E, int has_cls, int levels, int act_dtype, void* stream);
+size_t spectre_dwtmix_ml_bwd_workspace_bytes(int B, int H, int W, int E);
+
 /* ---------------------------------------------------------------------------------------------------
  * MHPermutMix gather -- the reference's HEAD occupant of the slot (spectre_vit/models/spectre/layers.py:68-70):
  *   mixed[b, h, j] = x.view(B, T*E)[b, perms[h, j]] * signs[h, j]            -> [B, heads, F], F = T*E

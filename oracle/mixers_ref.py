@@ -197,6 +197,48 @@ def dwt_mix_bwd_ref(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, H: int, 
     return dx, (X * DY).sum(0)
 
 
+def haar_ml_inplace(g: torch.Tensor, levels: int, inverse: bool = False) -> torch.Tensor:
+    """J-level orthonormal 2-D Haar with the coefficients left IN PLACE on the lattice (``DWTForward(J=3,
+    wave="haar", mode="zero")``, dwt_experiments.py:56; H, W multiples of 2^J so no padding arises).  Level l works on
+    the 2x2 blocks (a b / c d) of the points whose coordinates are multiples of 2^(l-1): LL -> a, low-W/high-H -> c,
+    high-W/low-H -> b, HH -> d; the next level recurses on the LL points.  ``inverse`` undoes it (levels J..1)."""
+    out = g.clone()
+    order = range(levels, 0, -1) if inverse else range(1, levels + 1)
+    for l in order:
+        st, h = 1 << l, 1 << (l - 1)
+        a, b = out[:, 0::st, 0::st].clone(), out[:, 0::st, h::st].clone()
+        c, d = out[:, h::st, 0::st].clone(), out[:, h::st, h::st].clone()
+        if inverse:                      # stored (ll, s2, s1, hh) at (a, b, c, d)
+            ll, s2, s1, hh = a, b, c, d
+            out[:, 0::st, 0::st] = (ll + s1 + s2 + hh) / 2
+            out[:, 0::st, h::st] = (ll + s1 - s2 - hh) / 2
+            out[:, h::st, 0::st] = (ll - s1 + s2 - hh) / 2
+            out[:, h::st, h::st] = (ll - s1 - s2 + hh) / 2
+        else:
+            out[:, 0::st, 0::st] = (a + b + c + d) / 2
+            out[:, h::st, 0::st] = (a + b - c - d) / 2     # low along W, high along H
+            out[:, 0::st, h::st] = (a - b + c - d) / 2     # high along W, low along H
+            out[:, h::st, h::st] = (a - b - c + d) / 2
+    return out
+
+
+def dwt_ml_mix_ref(x: torch.Tensor, w: torch.Tensor, H: int, W: int, levels: int) -> torch.Tensor:
+    """y = cat(cls, T^-1(w * T(grid))), T = ``levels``-level Haar; w real ``[H, W, E]`` (in-place layout)."""
+    B, T, E = x.shape
+    assert T == 1 + H * W and H % (1 << levels) == 0 and W % (1 << levels) == 0
+    y = haar_ml_inplace(haar_ml_inplace(x[:, 1:].reshape(B, H, W, E), levels) * w, levels, inverse=True)
+    return torch.cat([x[:, :1], y.reshape(B, H * W, E)], dim=1)
+
+
+def dwt_ml_mix_bwd_ref(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, H: int, W: int, levels: int):
+    """dx = T^-1(w * T dy) (T orthogonal); dw = sum_b T(x_b) * T(dy_b)."""
+    B, T, E = x.shape
+    DY = haar_ml_inplace(dy[:, 1:].reshape(B, H, W, E), levels)
+    X = haar_ml_inplace(x[:, 1:].reshape(B, H, W, E), levels)
+    dxg = haar_ml_inplace(DY * w, levels, inverse=True)
+    return torch.cat([dy[:, :1], dxg.reshape(B, H * W, E)], dim=1), (X * DY).sum(0)
+
+
 def haar2d_filterbank(g: torch.Tensor) -> torch.Tensor:
     """The same transform written as the published pywt/pytorch_wavelets Haar
     filter bank (``lo=[1,1]/sqrt2``, ``hi=[1,-1]/sqrt2``, stride 2, no padding

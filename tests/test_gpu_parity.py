@@ -127,6 +127,56 @@ def test_dwtmix_fwd_bwd(cuda_device, B, H, W, E, dtype, has_cls):
         assert torch.equal(y[:, 0].cpu(), x[:, 0])
 
 
+@pytest.mark.parametrize("B,H,W,E,levels,dtype", [
+    (16, 8, 8, 512, 3, torch.bfloat16),      # C3 grid with the reference call site's J=3
+    (5, 8, 8, 64, 3, torch.float32),
+    (3, 8, 8, 48, 2, torch.float32),         # ragged channel tile (48 = 32 + 16)
+    (4, 16, 16, 32, 4, torch.float32),
+    (300, 4, 8, 8, 2, torch.bfloat16),       # more images than slabs, non-square
+    (2, 8, 8, 16, 1, torch.float32),
+])
+@pytest.mark.parametrize("has_cls", [True, False])
+def test_dwtmix_multilevel_fwd_bwd(cuda_device, B, H, W, E, levels, dtype, has_cls):
+    """Multi-level Haar mixer through the C-ABI vs the oracle (in-place coefficient layout)."""
+    from vit_spectre_experiments_b200 import dwt_mix_ml
+
+    g = torch.Generator().manual_seed(7 + B + E + levels)
+    T = H * W + int(has_cls)
+    x = torch.randn(B, T, E, generator=g).to(dtype)
+    dy = torch.randn(B, T, E, generator=g).to(dtype)
+    w = 1.0 + 0.5 * torch.randn(H, W, E, generator=g)
+    xd, wd = x.to(cuda_device).requires_grad_(True), w.to(cuda_device).requires_grad_(True)
+    y = dwt_mix_ml(xd, wd, (H, W), has_cls, levels)
+    y.backward(dy.to(cuda_device))
+    xr, dyr = x.float(), dy.float()
+    if not has_cls:      # the oracle wants a CLS row: prepend a dummy one
+        xr = torch.cat([torch.zeros(B, 1, E), xr], 1)
+        dyr = torch.cat([torch.zeros(B, 1, E), dyr], 1)
+    y_ref = O.dwt_ml_mix_ref(xr, w, H, W, levels)
+    dx_ref, dw_ref = O.dwt_ml_mix_bwd_ref(dyr, xr, w, H, W, levels)
+    if not has_cls:
+        y_ref, dx_ref = y_ref[:, 1:], dx_ref[:, 1:]
+    tol = TOL[dtype]
+    assert y.dtype == dtype and rel_err(y, y_ref.to(dtype)) <= tol
+    assert rel_err(xd.grad, dx_ref.to(dtype)) <= tol
+    assert rel_err(wd.grad, dw_ref) <= (2e-5 if dtype == torch.float32 else 2e-3)
+    if has_cls:
+        assert torch.equal(y[:, 0].cpu(), x[:, 0]) and torch.equal(xd.grad[:, 0].cpu(), dy[:, 0])
+
+
+def test_multilevel_haar_module(cuda_device):
+    from vit_spectre_experiments_b200 import HaarDWTMix
+
+    m = HaarDWTMix(64, 65, 4, 64, levels=3).to(cuda_device)
+    assert tuple(m.weight.shape) == (8, 8, 64)
+    with torch.no_grad():
+        m.weight.fill_(1.0)
+    x = torch.randn(4, 65, 64, device=cuda_device)
+    assert rel_err(m(x), x) <= 1e-6           # unit weights: perfect reconstruction
+    with pytest.raises(ValueError):
+        HaarDWTMix(64, 197, 4, 64, levels=2)  # 14x14 is not a multiple of 4
+
+
 def test_identity_filter_and_linearity_full_size(cuda_device):
     """Size-independent properties at BASELINE.json's full C4 shape ([256,197,384] bf16):
     identity filter => y == x (up to bf16 rounding of an exact round trip); linearity in x."""

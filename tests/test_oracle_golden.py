@@ -135,3 +135,36 @@ def test_oracle_dwt_odd_grid_zero_mode(H, W):
     gx, gw = torch.autograd.grad(y, (x, w), dy)
     dx, dw = O.dwt_mix_bwd_ref(dy, x.detach(), w.detach(), H, W)
     assert (dx - gx).abs().max() < 1e-12 and (dw - gw).abs().max() < 1e-12
+
+
+def test_oracle_multilevel_haar_layout_and_recursion():
+    """The in-place multi-level Haar of the oracle: (i) one level == the single-level oracle under the documented
+    de-interleaving; (ii) J levels == recursing the single-level transform on the LL band (the Mallat pyramid the
+    reference's DWTForward(J=3) computes); (iii) inverse undoes it; (iv) closed-form backward == autograd."""
+    import torch
+
+    from oracle import mixers_ref as O
+
+    torch.manual_seed(8)
+    B, H, W, E = 2, 8, 8, 4
+    g = torch.randn(B, H, W, E, dtype=torch.float64)
+    one = O.haar_ml_inplace(g, 1)
+    s4 = O.haar2d(g)                                   # [B, 4, H/2, W/2, E]: LL, lowW/highH, highW/lowH, HH
+    assert torch.allclose(one[:, 0::2, 0::2], s4[:, 0]) and torch.allclose(one[:, 1::2, 0::2], s4[:, 1])
+    assert torch.allclose(one[:, 0::2, 1::2], s4[:, 2]) and torch.allclose(one[:, 1::2, 1::2], s4[:, 3])
+    three = O.haar_ml_inplace(g, 3)
+    ll1 = s4[:, 0]
+    s4b = O.haar2d(ll1)                                # level 2 on the LL band
+    assert torch.allclose(three[:, 2::4, 0::4], s4b[:, 1]) and torch.allclose(three[:, 0::4, 2::4], s4b[:, 2])
+    assert torch.allclose(three[:, 2::4, 2::4], s4b[:, 3])
+    s4c = O.haar2d(s4b[:, 0])                          # level 3
+    assert torch.allclose(three[:, 0::8, 0::8], s4c[:, 0]) and torch.allclose(three[:, 4::8, 4::8], s4c[:, 3])
+    assert torch.allclose(three[:, 1::2, 1::2], s4[:, 3])          # level-1 details untouched by later levels
+    assert torch.allclose(O.haar_ml_inplace(three, 3, inverse=True), g)
+    assert abs(three.pow(2).sum() - g.pow(2).sum()) < 1e-9         # orthonormal
+    x = torch.randn(B, 1 + H * W, E, dtype=torch.float64, requires_grad=True)
+    w = (1 + 0.3 * torch.randn(H, W, E, dtype=torch.float64)).requires_grad_(True)
+    dy = torch.randn(B, 1 + H * W, E, dtype=torch.float64)
+    gx, gw = torch.autograd.grad(O.dwt_ml_mix_ref(x, w, H, W, 3), (x, w), dy)
+    dx, dw = O.dwt_ml_mix_bwd_ref(dy, x.detach(), w.detach(), H, W, 3)
+    assert (dx - gx).abs().max() < 1e-12 and (dw - gw).abs().max() < 1e-12

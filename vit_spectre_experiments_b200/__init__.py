@@ -7,7 +7,7 @@ Public surface
 ``SpectreViT`` / ``SpectreEncoderLayer`` host-side mirror of the reference model classes with a
                                          ``mixer=`` switch at the one line that builds ``mix_layer``
 """
-from .functional import dwt_mix, fft_mix  # noqa: F401
+from .functional import dwt_mix, dwt_mix_ml, fft_mix  # noqa: F401
 from .mixers import FNetMix, HaarDWTMix, SpectralFilterMix  # noqa: F401
 from .model import (  # noqa: F401
     MHPermutMix,

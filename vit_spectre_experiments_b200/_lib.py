@@ -20,6 +20,9 @@ EXPORTED_SYMBOLS = (
     "spectre_dwtmix_fwd",
     "spectre_dwtmix_bwd",
     "spectre_dwtmix_bwd_workspace_bytes",
+    "spectre_dwtmix_ml_fwd",
+    "spectre_dwtmix_ml_bwd",
+    "spectre_dwtmix_ml_bwd_workspace_bytes",
     "spectre_norm_act_fwd",
     "spectre_norm_act_bwd",
     "spectre_norm_act_bwd_workspace_bytes",
@@ -66,6 +69,12 @@ def load() -> ctypes.CDLL:
                 "Build it with `python -m vit_spectre_experiments_b200.build` (needs nvcc)."
             )
         lib = ctypes.CDLL(LIB_PATH)
+        lib.spectre_dwtmix_ml_fwd.argtypes = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_dwtmix_ml_fwd.restype = _i
+        lib.spectre_dwtmix_ml_bwd.argtypes = [_p, _p, _p, _p, _p, _p, _sz, _i, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_dwtmix_ml_bwd.restype = _i
+        lib.spectre_dwtmix_ml_bwd_workspace_bytes.argtypes = [_i, _i, _i, _i]
+        lib.spectre_dwtmix_ml_bwd_workspace_bytes.restype = _sz
         lib.spectre_debug_mark_main_kernel_end.argtypes = [_p]
         lib.spectre_debug_mark_main_kernel_end.restype = None
         lib.spectre_debug_mark_pending.argtypes = []

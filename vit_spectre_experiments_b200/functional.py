@@ -246,3 +246,58 @@ def dwt_mix(x: torch.Tensor, weight: torch.Tensor, grid, has_cls: bool = True) -
     """
     H, W = grid
     return _Mix.apply(x, weight, "dwt", int(H), int(W), bool(has_cls))
+
+
+class _DwtMl(torch.autograd.Function):
+    """Multi-level Haar mixer (``spectre_dwtmix_ml_fwd/bwd``); weight float32 ``[H, W, E]`` in the in-place layout."""
+
+    @staticmethod
+    def forward(ctx, x, weight, H, W, has_cls, levels):
+        lib = _lib.load()
+        what = "dwt_mix_ml"
+        _check_tokens(x, H, W, has_cls, what)
+        code = _act_code(x, what)
+        B, _, E = x.shape
+        if weight.dtype != torch.float32 or tuple(weight.shape) != (H, W, E):
+            raise RuntimeError(f"{what}: weight must be float32 {[H, W, E]}, got {weight.dtype} {tuple(weight.shape)}")
+        x = x.contiguous()
+        w = weight.detach().contiguous()
+        y = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            with _timed("dwtmlmix_fwd", (B, H, W, E, x.element_size())):
+                rc = lib.spectre_dwtmix_ml_fwd(x.data_ptr(), w.data_ptr(), y.data_ptr(), B, H, W, E, int(has_cls),
+                                               int(levels), code, _stream_ptr(x.device))
+        _lib.check(rc, "spectre_dwtmix_ml_fwd")
+        _lib.count_launches()
+        ctx.save_for_backward(x, w)
+        ctx.meta = (H, W, has_cls, levels)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _lib.load()
+        x, w = ctx.saved_tensors
+        H, W, has_cls, levels = ctx.meta
+        B, _, E = x.shape
+        dy = dy.to(x.dtype).contiguous()
+        dx, dw = torch.empty_like(x), torch.empty_like(w)
+        with torch.cuda.device(x.device):
+            nbytes = lib.spectre_dwtmix_ml_bwd_workspace_bytes(B, H, W, E)
+            ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
+            with _timed("dwtmlmix_bwd", (B, H, W, E, x.element_size()), mark_main=True):
+                rc = lib.spectre_dwtmix_ml_bwd(dy.data_ptr(), x.data_ptr(), w.data_ptr(), dx.data_ptr(), dw.data_ptr(),
+                                               ws.data_ptr(), nbytes, B, H, W, E, int(has_cls), int(levels),
+                                               _act_code(x, "dwt_mix_ml"), _stream_ptr(x.device))
+        _lib.check(rc, "spectre_dwtmix_ml_bwd")
+        _lib.count_launches()
+        return dx, dw, None, None, None, None
+
+
+def dwt_mix_ml(x: torch.Tensor, weight: torch.Tensor, grid, has_cls: bool = True, levels: int = 3) -> torch.Tensor:
+    """``cat(cls, T^-1(weight * T(x_grid)))`` with ``T`` the ``levels``-level orthonormal 2-D Haar transform
+    (``DWTForward(J=3, wave="haar", mode="zero")``, dwt_experiments.py:56), one fused CUDA pass.
+
+    weight float32 ``[H, W, E]``: coefficients addressed in place on the token lattice (include/spectre_b200.h).
+    """
+    H, W = grid
+    return _DwtMl.apply(x, weight, int(H), int(W), bool(has_cls), int(levels))

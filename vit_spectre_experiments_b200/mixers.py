@@ -14,7 +14,7 @@ import math
 import torch
 import torch.nn as nn
 
-from .functional import dwt_mix, fft_mix
+from .functional import dwt_mix, dwt_mix_ml, fft_mix
 
 
 def _resolve_grid(token_dim: int, grid, has_cls: bool):
@@ -90,6 +90,8 @@ class HaarDWTMix(_Fp32ParamMixin, nn.Module):
 
     Parameter ``weight``: float32 ``[4, ceil(H/2), ceil(W/2), E]`` ordered (LL, W-low/H-high, W-high/H-low, HH).
     Odd grids follow ``mode="zero"`` (dwt_experiments.py:56): zero row / column appended, result cropped.
+    ``levels > 1``: multi-level transform, ``weight`` float32 ``[H, W, E]`` with the coefficients addressed in place on
+    the token lattice (include/spectre_b200.h, ``spectre_dwtmix_ml_fwd``).
     """
 
     _fp32_param = "weight"
@@ -99,16 +101,23 @@ class HaarDWTMix(_Fp32ParamMixin, nn.Module):
         super().__init__()
         if out_channels != embed_dim:
             raise ValueError("HaarDWTMix keeps the channel count: out_channels must equal embed_dim")
-        if levels != 1:
-            raise NotImplementedError("only a single decomposition level is implemented")
         self.embed_dim, self.token_dim, self.num_heads = embed_dim, token_dim, num_heads
         self.has_cls = bool(has_cls)
+        self.levels = int(levels)
         self.grid = _resolve_grid(token_dim, grid, self.has_cls)
         H, W = self.grid
-        self.weight = nn.Parameter(1.0 + init_std * torch.randn(4, (H + 1) // 2, (W + 1) // 2, embed_dim))
+        if self.levels == 1:
+            self.weight = nn.Parameter(1.0 + init_std * torch.randn(4, (H + 1) // 2, (W + 1) // 2, embed_dim))
+        else:
+            # J levels (the reference call site uses J=3): coefficients in place on the token lattice, [H, W, E]
+            if self.levels < 1 or H % (1 << self.levels) or W % (1 << self.levels):
+                raise ValueError(f"levels={levels} needs H and W to be multiples of 2^levels, got {H}x{W}")
+            self.weight = nn.Parameter(1.0 + init_std * torch.randn(H, W, embed_dim))
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return dwt_mix(self._activation(x), self.weight, self.grid, self.has_cls)
+        if self.levels == 1:
+            return dwt_mix(self._activation(x), self.weight, self.grid, self.has_cls)
+        return dwt_mix_ml(self._activation(x), self.weight, self.grid, self.has_cls, self.levels)
 
     def extra_repr(self) -> str:
         return f"embed_dim={self.embed_dim}, grid={self.grid}, has_cls={self.has_cls}"

@@ -165,7 +165,7 @@ class SpectreEncoderLayer(nn.Module):
         s1 = _dropout_seed() if p1 > 0 else 0
         s2 = _dropout_seed() if p2 > 0 else 0
         mix = self.mix_layer
-        if isinstance(mix, (SpectralFilterMix, HaarDWTMix)) and x.dim() == 3:
+        if isinstance(mix, (SpectralFilterMix, HaarDWTMix)) and x.dim() == 3 and getattr(mix, "levels", 1) == 1:
             kind, param = ("fft", mix.filter) if isinstance(mix, SpectralFilterMix) else ("dwt", mix.weight)
             return encoder_layer(x, kind, param, mix.grid, mix.has_cls, self.norm1, lin1, ln1, lin3, ln3, self.norm2,
                                  p1, p2, s1, s2, x_twin=x_twin, return_twin=return_twin)
