@@ -29,6 +29,8 @@ SHAPES = [
     ("C3 dwt 8x8 E512 bf16 B1024", "dwt", 1024, 8, 8, 512, torch.bfloat16),
     ("dwt 8x8 E512 f32 B1024", "dwt", 1024, 8, 8, 512, torch.float32),
     ("dwt 14x14 E384 bf16 B256", "dwt", 256, 14, 14, 384, torch.bfloat16),
+    ("C3 dwtml J3 8x8 E512 bf16 B1024", "dwtml", 1024, 8, 8, 512, torch.bfloat16),
+    ("dwtml J3 8x8 E512 f32 B1024", "dwtml", 1024, 8, 8, 512, torch.float32),
     ("C4 14x14 E384 bf16 B256", "fft", 256, 14, 14, 384, torch.bfloat16),
     ("C4-shape 14x14 E384 f32 B256", "fft", 256, 14, 14, 384, torch.float32),
     ("C5 14x14 E768 bf16 B128", "fft", 128, 14, 14, 768, torch.bfloat16),
@@ -77,6 +79,9 @@ def main():
         if kind == "fft":
             p = torch.randn(H, W // 2 + 1, E, 2, device=dev)
             nws = lib.spectre_fftmix_bwd_workspace_bytes(B, H, W, E)
+        elif kind == "dwtml":
+            p = torch.randn(H, W, E, device=dev)
+            nws = lib.spectre_dwtmix_ml_bwd_workspace_bytes(B, H, W, E)
         else:
             p = torch.randn(4, H // 2, W // 2, E, device=dev)
             nws = lib.spectre_dwtmix_bwd_workspace_bytes(B, H, W, E)
@@ -86,6 +91,9 @@ def main():
         if kind == "fft":
             fwd = lambda: _lib.check(lib.spectre_fftmix_fwd(x.data_ptr(), p.data_ptr(), y.data_ptr(), B, H, W, E, 1, code, st()), "fwd")
             bwd = lambda: _lib.check(lib.spectre_fftmix_bwd(dy.data_ptr(), x.data_ptr(), p.data_ptr(), dx.data_ptr(), dp.data_ptr(), ws.data_ptr(), nws, B, H, W, E, 1, code, st()), "bwd")
+        elif kind == "dwtml":
+            fwd = lambda: _lib.check(lib.spectre_dwtmix_ml_fwd(x.data_ptr(), p.data_ptr(), y.data_ptr(), B, H, W, E, 1, 3, code, st()), "fwd")
+            bwd = lambda: _lib.check(lib.spectre_dwtmix_ml_bwd(dy.data_ptr(), x.data_ptr(), p.data_ptr(), dx.data_ptr(), dp.data_ptr(), ws.data_ptr(), nws, B, H, W, E, 1, 3, code, st()), "bwd")
         else:
             fwd = lambda: _lib.check(lib.spectre_dwtmix_fwd(x.data_ptr(), p.data_ptr(), y.data_ptr(), B, H, W, E, 1, code, st()), "fwd")
             bwd = lambda: _lib.check(lib.spectre_dwtmix_bwd(dy.data_ptr(), x.data_ptr(), p.data_ptr(), dx.data_ptr(), dp.data_ptr(), ws.data_ptr(), nws, B, H, W, E, 1, code, st()), "bwd")

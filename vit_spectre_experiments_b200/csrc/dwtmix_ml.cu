@@ -15,6 +15,8 @@
 // for 8x8, 32 KB for 16x16; the backward holds x and dy: twice that), levels are separated by CTA barriers, weight
 // gradients accumulate in registers (a thread always meets the same (position, channel) elements) and leave as one
 // partial slab per image slab, reduced in a fixed order by launch_reduce_partials (deterministic).
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace sb200 {
@@ -23,7 +25,7 @@ namespace {
 
 constexpr int kMlTile = 32;      // channels per CTA
 constexpr int kMlThreads = 256;
-constexpr int kMlMaxPerThread = 32;   // H*W*32 / 256 with H*W <= 256
+constexpr int kMlMaxPerThread = 32;   // H*W*32 / 256 with H*W <= 256 (kernels are instantiated for 4, 8, 16, 32)
 
 template <class T>
 __device__ __forceinline__ float ml_ld(const T* p);
@@ -40,10 +42,11 @@ __device__ __forceinline__ void ml_st(__nv_bfloat16* p, float v) { *p = __float2
 template <bool kTwo>
 __device__ __forceinline__ void ml_level(float* A, float* Bf, int H, int W, int level, bool inverse) {
   const int step = 1 << level, half = step >> 1;
-  const int bw = W / step, items = (H / step) * bw * kMlTile;
+  const int bw = W >> level, items = (H >> level) * bw * kMlTile;
   for (int it = threadIdx.x; it < items; it += kMlThreads) {
     const int c = it % kMlTile, blk = it / kMlTile;
-    const int r0 = (blk / bw) * step, q0 = (blk % bw) * step;
+    const int br = blk / bw;
+    const int r0 = br << level, q0 = (blk - br * bw) << level;
     const int pa = (r0 * W + q0) * kMlTile + c, pb = pa + half * kMlTile, pc = pa + half * W * kMlTile,
               pd = pc + half * kMlTile;
     const int i1 = inverse ? pc : pb, i2 = inverse ? pb : pc;   // second / third operand of the butterfly
@@ -63,8 +66,8 @@ __device__ __forceinline__ void ml_level(float* A, float* Bf, int H, int W, int 
   __syncthreads();
 }
 
-template <class T, bool kBackward>
-__global__ void __launch_bounds__(kMlThreads) dwtml_kernel(const T* __restrict__ in, const T* __restrict__ xsave,
+template <class T, bool kBackward, int KMAX>   // KMAX >= elements per thread = H*W*32 / 256
+__global__ void __launch_bounds__(kMlThreads, KMAX <= 8 ? 4 : 2) dwtml_kernel(const T* __restrict__ in, const T* __restrict__ xsave,
                                                            const float* __restrict__ wgt, T* __restrict__ out,
                                                            float* __restrict__ part, int B, int H, int W, int E, int cls,
                                                            int levels) {
@@ -73,27 +76,41 @@ __global__ void __launch_bounds__(kMlThreads) dwtml_kernel(const T* __restrict__
   float* A = sm;                       // the tile being mixed (x forward, dy backward)
   float* X = sm + n;                   // backward: the saved x
   const int c0 = blockIdx.x * kMlTile;
-  float acc[kMlMaxPerThread];
+  float acc[KMAX];
   if (kBackward) {
 #pragma unroll
-    for (int k = 0; k < kMlMaxPerThread; ++k) acc[k] = 0.f;
+    for (int k = 0; k < KMAX; ++k) acc[k] = 0.f;
   }
 
   for (int b = blockIdx.y; b < B; b += gridDim.y) {
     const size_t base = static_cast<size_t>(b) * tokens * E;
-    for (int idx = threadIdx.x; idx < n; idx += kMlThreads) {
-      const int c = c0 + idx % kMlTile, pos = idx / kMlTile;
-      const bool live = c < E;
-      const size_t off = base + static_cast<size_t>(cls + pos) * E + c;
-      A[idx] = live ? ml_ld<T>(in + off) : 0.f;
-      if (kBackward) X[idx] = live ? ml_ld<T>(xsave + off) : 0.f;
+    {   // all of the thread's loads are issued before the first shared-memory store (one DRAM round trip per image,
+        // not one per element)
+      float v[KMAX], vx[kBackward ? KMAX : 1];
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) {
+        const int idx = threadIdx.x + k * kMlThreads;
+        const int c = c0 + idx % kMlTile, pos = idx / kMlTile;
+        const bool live = idx < n && c < E;
+        const size_t off = base + static_cast<size_t>(cls + pos) * E + c;
+        v[k] = live ? ml_ld<T>(in + off) : 0.f;
+        if (kBackward) vx[k] = live ? ml_ld<T>(xsave + off) : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) {
+        const int idx = threadIdx.x + k * kMlThreads;
+        if (idx < n) {
+          A[idx] = v[k];
+          if (kBackward) X[idx] = vx[k];
+        }
+      }
     }
     if (cls && threadIdx.x < kMlTile && c0 + threadIdx.x < E)
       ml_st(out + base + c0 + threadIdx.x, ml_ld<T>(in + base + c0 + threadIdx.x));
     __syncthreads();
     for (int l = 1; l <= levels; ++l) ml_level<kBackward>(A, X, H, W, l, false);
 #pragma unroll
-    for (int k = 0; k < kMlMaxPerThread; ++k) {
+    for (int k = 0; k < KMAX; ++k) {
       const int idx = threadIdx.x + k * kMlThreads;
       if (idx < n) {
         const int c = c0 + idx % kMlTile, pos = idx / kMlTile;
@@ -115,7 +132,7 @@ __global__ void __launch_bounds__(kMlThreads) dwtml_kernel(const T* __restrict__
   if (kBackward) {
     float* slab = part + static_cast<size_t>(blockIdx.y) * HW * E;
 #pragma unroll
-    for (int k = 0; k < kMlMaxPerThread; ++k) {
+    for (int k = 0; k < KMAX; ++k) {
       const int idx = threadIdx.x + k * kMlThreads;
       if (idx < n) {
         const int c = c0 + idx % kMlTile, pos = idx / kMlTile;
@@ -127,7 +144,7 @@ __global__ void __launch_bounds__(kMlThreads) dwtml_kernel(const T* __restrict__
 
 int ml_slabs(int B, int E) {
   const int ctas_x = (E + kMlTile - 1) / kMlTile;
-  int ny = (device_sm_count() * 4 + ctas_x - 1) / ctas_x;
+  int ny = (device_sm_count() * 8 + ctas_x - 1) / ctas_x;
   if (ny < 1) ny = 1;
   if (ny > B) ny = B;
   return ny;
@@ -140,27 +157,38 @@ int ml_launch(bool backward, const void* in, const void* xsave, const float* w, 
   const dim3 grid((E + kMlTile - 1) / kMlTile, ny);
   const size_t smem = static_cast<size_t>(backward ? 2 : 1) * H * W * kMlTile * sizeof(float);
   last_launch_count() = 1;
-  if (!backward) {
-    static const cudaError_t attr = cudaFuncSetAttribute(reinterpret_cast<const void*>(dwtml_kernel<T, false>),
-                                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-    (void)attr;
-    dwtml_kernel<T, false><<<grid, kMlThreads, smem, st>>>(static_cast<const T*>(in), nullptr, w, static_cast<T*>(out),
-                                                           nullptr, B, H, W, E, cls, levels);
-  } else {
-    static const cudaError_t attr = cudaFuncSetAttribute(reinterpret_cast<const void*>(dwtml_kernel<T, true>),
-                                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-    (void)attr;
+  const int per = (H * W * kMlTile + kMlThreads - 1) / kMlThreads;
+  float* part = nullptr;
+  if (backward) {
     const size_t slab_floats = static_cast<size_t>(H) * W * E;
     if (ny > 1 && ws_bytes < slab_floats * sizeof(float) * ny)
       return fail(SPECTRE_E_WORKSPACE, "dwtmix_ml_bwd: workspace %zu B < required %zu B", ws_bytes,
                   slab_floats * sizeof(float) * ny);
-    float* part = ny > 1 ? static_cast<float*>(ws) : dw;
-    dwtml_kernel<T, true><<<grid, kMlThreads, smem, st>>>(static_cast<const T*>(in), static_cast<const T*>(xsave), w,
-                                                          static_cast<T*>(out), part, B, H, W, E, cls, levels);
-    if (ny > 1) {
-      launch_reduce_partials(part, dw, slab_floats, ny, st);
-      last_launch_count() = 2;
+    part = ny > 1 ? static_cast<float*>(ws) : dw;
+  }
+  auto go = [&](auto kmax) {
+    constexpr int K = decltype(kmax)::value;
+    if (backward) {
+      static const cudaError_t attr = cudaFuncSetAttribute(reinterpret_cast<const void*>(dwtml_kernel<T, true, K>),
+                                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+      (void)attr;
+      dwtml_kernel<T, true, K><<<grid, kMlThreads, smem, st>>>(static_cast<const T*>(in), static_cast<const T*>(xsave), w,
+                                                               static_cast<T*>(out), part, B, H, W, E, cls, levels);
+    } else {
+      static const cudaError_t attr = cudaFuncSetAttribute(reinterpret_cast<const void*>(dwtml_kernel<T, false, K>),
+                                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+      (void)attr;
+      dwtml_kernel<T, false, K><<<grid, kMlThreads, smem, st>>>(static_cast<const T*>(in), nullptr, w, static_cast<T*>(out),
+                                                                nullptr, B, H, W, E, cls, levels);
     }
+  };
+  if (per <= 4) go(std::integral_constant<int, 4>{});
+  else if (per <= 8) go(std::integral_constant<int, 8>{});
+  else if (per <= 16) go(std::integral_constant<int, 16>{});
+  else go(std::integral_constant<int, kMlMaxPerThread>{});
+  if (backward && ny > 1) {
+    launch_reduce_partials(part, dw, static_cast<size_t>(H) * W * E, ny, st);
+    last_launch_count() = 2;
   }
   const cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "dwtmix_ml launch: %s", cudaGetErrorString(err));
