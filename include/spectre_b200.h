@@ -116,6 +116,10 @@ typedef struct spectre_norm_act_t {
 int spectre_norm_act_fwd(const spectre_norm_act_t* desc, void* stream);
 int spectre_norm_act_bwd(const spectre_norm_act_t* desc, void* stream);
 size_t spectre_norm_act_bwd_workspace_bytes(long long rows, int N);
+/* 1 if rows of width N with a skip of width Ns (pass Ns = N for none) fit the kernels in both directions
+ * (N, Ns multiples of 8, N <= 4096, Ns <= 16384, shared-memory budget), else 0: callers keep the stock
+ * torch composition for such widths. */
+int spectre_norm_act_supported(int N, int Ns, int act_dtype);
 
 /* Multi-level Haar DWT mixer (J = levels, the reference call site uses J=3: dwt_experiments.py:56; H and W multiples
  * of 2^levels, H*W <= 256, E a multiple of 4):  y[:,1:] = T^-1( w * T(x[:,1:]) ), T = J-level orthonormal 2-D Haar.

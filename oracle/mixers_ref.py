@@ -86,7 +86,7 @@ def fft_mix_bwd_ref(dy: torch.Tensor, x: torch.Tensor, filt: torch.Tensor, H: in
     DY = torch.fft.rfft2(dy[:, 1:].reshape(B, H, W, E), dim=(1, 2), norm="ortho")
     X = torch.fft.rfft2(x[:, 1:].reshape(B, H, W, E), dim=(1, 2), norm="ortho")
     dxg = torch.fft.irfft2(f.conj() * DY, s=(H, W), dim=(1, 2), norm="ortho")
-    c = torch.full((Wh,), 2.0, dtype=x.dtype)
+    c = torch.full((Wh,), 2.0, dtype=x.dtype, device=x.device)
     c[0] = 1.0
     if W % 2 == 0:
         c[-1] = 1.0

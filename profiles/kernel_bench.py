@@ -118,6 +118,12 @@ NA_SHAPES = [
     ("C4 GELU(LN(h2))+down N384", 256 * 197, 384, 1536, False, "gelu", 0.001, torch.bfloat16),
     ("C4 LN2(x1+ff) N384", 256 * 197, 384, None, True, "none", 0.0, torch.bfloat16),
     ("C4 GELU(LN(h1))+up N1536 f32", 256 * 197, 1536, 384, False, "gelu", 0.001, torch.float32),
+    ("C4 bench B2048 LN1(mix)+x N384", 2048 * 197, 384, 384, False, "none", 0.0, torch.bfloat16),
+    ("C4 bench B2048 GELU(LN(h1))+up N1536", 2048 * 197, 1536, 384, False, "gelu", 0.001, torch.bfloat16),
+    ("C4 bench B2048 GELU(LN(h2))+down N384", 2048 * 197, 384, 1536, False, "gelu", 0.001, torch.bfloat16),
+    ("C4 bench B2048 LN2(x1+ff) N384", 2048 * 197, 384, None, True, "none", 0.0, torch.bfloat16),
+    ("C5 B512 GELU(LN(h1))+up N3072", 512 * 197, 3072, 768, False, "gelu", 0.001, torch.bfloat16),
+    ("C5 B512 GELU(LN(h2))+down N768", 512 * 197, 768, 3072, False, "gelu", 0.001, torch.bfloat16),
     ("C3 GELU(LN(h1))+general 512->768", 1024 * 65, 768, 512, False, "gelu", 0.001, torch.bfloat16),
     ("C3 GELU(LN(h2))+general 768->512", 1024 * 65, 512, 768, False, "gelu", 0.001, torch.bfloat16),
     ("C2 GELU(LN(h1))+general 48->256 f32", 4096 * 50, 256, 48, False, "gelu", 0.001, torch.float32),

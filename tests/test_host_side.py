@@ -168,3 +168,38 @@ def test_fnet_mixer_in_the_model():
     out = net(torch.randn(2, 3, 32, 32))
     assert out.shape == (2, 10) and torch.isfinite(out).all()
     out.sum().backward()
+
+
+def test_permut_inverse_cache_follows_load_state_dict():
+    """``load_state_dict`` copies into ``perms`` in place; the cached inverse permutations (CUDA backward of
+    the ``permut`` mixer) must be rebuilt, not reused."""
+    from vit_spectre_experiments_b200.functional import inverse_permutations
+    from vit_spectre_experiments_b200.model import MHPermutMix
+
+    torch.manual_seed(0)
+    a, b = MHPermutMix(8, 5, 2, 8), MHPermutMix(8, 5, 2, 8)
+    assert not torch.equal(a.perms, b.perms)
+    assert torch.equal(a._inverse(), inverse_permutations(a.perms))
+    a.load_state_dict(b.state_dict())
+    assert torch.equal(a.perms, b.perms)
+    assert torch.equal(a._inverse(), inverse_permutations(b.perms))
+    first = a._inverse()
+    assert a._inverse() is first            # unchanged buffer: the cache is used
+
+
+def test_mixer_construction_validates_grid_and_widths():
+    """unsupported grids fail at construction with a clear message; layer widths the fused row-wise kernels
+    cannot take are detected by the ``spectre_norm_act_supported`` query (the layer then keeps the torch composition)."""
+    import pytest
+
+    from vit_spectre_experiments_b200 import HaarDWTMix, SpectralFilterMix, _lib
+
+    with pytest.raises(ValueError, match="no CUDA kernel"):
+        SpectralFilterMix(16, 26, 2, 16)                      # 5x5 grid: not compiled
+    SpectralFilterMix(16, 50, 2, 16)                          # 7x7 is
+    with pytest.raises(ValueError, match="H\\*W <= 256"):
+        HaarDWTMix(16, 1 + 32 * 32, 2, 16, levels=2)
+    lib = _lib.load()
+    assert lib.spectre_norm_act_supported(384, 1536, 1) == 1 and lib.spectre_norm_act_supported(1536, 384, 0) == 1
+    assert lib.spectre_norm_act_supported(5120, 5120, 0) == 0 and lib.spectre_norm_act_supported(12, 12, 0) == 0
+    assert lib.spectre_norm_act_supported(512, 768, 1) == 1 and lib.spectre_norm_act_supported(48, 256, 0) == 1

@@ -26,6 +26,7 @@ EXPORTED_SYMBOLS = (
     "spectre_norm_act_fwd",
     "spectre_norm_act_bwd",
     "spectre_norm_act_bwd_workspace_bytes",
+    "spectre_norm_act_supported",
     "spectre_permut_fwd",
     "spectre_permut_bwd",
     "spectre_debug_mark_main_kernel_end",
@@ -97,6 +98,8 @@ def load() -> ctypes.CDLL:
         lib.spectre_norm_act_bwd.restype = _i
         lib.spectre_norm_act_bwd_workspace_bytes.argtypes = [ctypes.c_longlong, _i]
         lib.spectre_norm_act_bwd_workspace_bytes.restype = _sz
+        lib.spectre_norm_act_supported.argtypes = [_i, _i, _i]
+        lib.spectre_norm_act_supported.restype = _i
         lib.spectre_permut_fwd.argtypes = [_p, _p, _p, _p, _i, ctypes.c_longlong, _i, _i, _p]
         lib.spectre_permut_fwd.restype = _i
         lib.spectre_permut_bwd.argtypes = [_p, _p, _p, _p, _i, ctypes.c_longlong, _i, _i, _p]

@@ -1,6 +1,8 @@
 // extern "C" entry points declared in include/spectre_b200.h: argument validation,
 // error bookkeeping, dispatch to the templated launchers.  No torch types here.
 #include <cstdarg>
+#include <mutex>
+#include <unordered_map>
 
 #include "common.cuh"
 
@@ -45,6 +47,21 @@ int device_sm_count() {
   return cached_sms > 0 ? cached_sms : 148;
 }
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+cudaError_t ensure_dynamic_smem(const void* kernel, int bytes) {
+  static std::mutex mu;
+  static std::unordered_map<const void*, unsigned long long> done[2];   // bit d (of word d / 64) = device d configured
+  int dev = 0;
+  if (cudaError_t e = cudaGetDevice(&dev); e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 128) return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  const unsigned long long bit = 1ull << (dev & 63);
+  std::lock_guard<std::mutex> lock(mu);
+  unsigned long long& mask = done[dev >> 6][kernel];
+  if (mask & bit) return cudaSuccess;
+  const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) mask |= bit;
+  return e;
+}
 
 // out[i] = sum_k part[k][i], float4 granularity.  CTA = 64 float4 columns x 4 slab lanes; a lane strides over the
 // slabs with four independent accumulators (16 loads in flight per column), the lanes are combined through shared

@@ -19,6 +19,9 @@ int& last_launch_count();
 int fail(int code, const char* fmt, ...);
 int device_sm_count();
 bool aligned16(const void* p);
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE function attribute: set it on the first use of
+// (kernel, current device) -- a process driving several GPUs must not rely on a once-per-process flag.
+cudaError_t ensure_dynamic_smem(const void* kernel, int bytes);
 
 // ------------------------------------------------------------------ channel-pair I/O
 // One thread moves two adjacent channels: a 64-bit access for fp32, a 32-bit

@@ -169,15 +169,11 @@ int ml_launch(bool backward, const void* in, const void* xsave, const float* w, 
   auto go = [&](auto kmax) {
     constexpr int K = decltype(kmax)::value;
     if (backward) {
-      static const cudaError_t attr = cudaFuncSetAttribute(reinterpret_cast<const void*>(dwtml_kernel<T, true, K>),
-                                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-      (void)attr;
+      ensure_dynamic_smem(reinterpret_cast<const void*>(dwtml_kernel<T, true, K>), 64 * 1024);
       dwtml_kernel<T, true, K><<<grid, kMlThreads, smem, st>>>(static_cast<const T*>(in), static_cast<const T*>(xsave), w,
                                                                static_cast<T*>(out), part, B, H, W, E, cls, levels);
     } else {
-      static const cudaError_t attr = cudaFuncSetAttribute(reinterpret_cast<const void*>(dwtml_kernel<T, false, K>),
-                                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-      (void)attr;
+      ensure_dynamic_smem(reinterpret_cast<const void*>(dwtml_kernel<T, false, K>), 64 * 1024);
       dwtml_kernel<T, false, K><<<grid, kMlThreads, smem, st>>>(static_cast<const T*>(in), nullptr, w, static_cast<T*>(out),
                                                                 nullptr, B, H, W, E, cls, levels);
     }

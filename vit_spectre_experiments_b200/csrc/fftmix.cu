@@ -282,12 +282,8 @@ static int fwd_launch(const void* x, const float* filt, void* y, int B, int E, i
   using S = Shape<H, W>;
   auto kern = fftmix_fwd_kernel<H, W, S::G_fwd, S::NT_fwd, T>;
   constexpr size_t smem = Smem<H, W>::fwd;
-  static bool configured = false;
-  if (!configured) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
-      return fail(SPECTRE_E_CUDA, "cudaFuncSetAttribute(fwd): %s", cudaGetErrorString(cudaGetLastError()));
-    configured = true;
-  }
+  if (ensure_dynamic_smem(reinterpret_cast<const void*>(kern), static_cast<int>(smem)) != cudaSuccess)
+    return fail(SPECTRE_E_CUDA, "cudaFuncSetAttribute(fwd): %s", cudaGetErrorString(cudaGetLastError()));
   const int tiles = (E + kTileC - 1) / kTileC;
   const int groups = (B + S::G_fwd - 1) / S::G_fwd;
   const int ny = pick_slabs(kern, S::NT_fwd, smem, tiles, groups);
@@ -302,11 +298,7 @@ template <int H, int W, class T>
 static int bwd_slabs(int B, int E) {
   using S = Shape<H, W>;
   auto kern = fftmix_bwd_kernel<H, W, S::G_bwd, S::NT_bwd, T>;
-  static bool configured = false;
-  if (!configured) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(Smem<H, W>::bwd));
-    configured = true;
-  }
+  ensure_dynamic_smem(reinterpret_cast<const void*>(kern), static_cast<int>(Smem<H, W>::bwd));
   const int tiles = (E + kTileC - 1) / kTileC;
   const int groups = (B + S::G_bwd - 1) / S::G_bwd;
   return pick_slabs(kern, S::NT_bwd, Smem<H, W>::bwd, tiles, groups);

@@ -651,12 +651,8 @@ static int fwd_launch(const void* x, const float* filt, void* y, int B, int E, i
   using C = Cfg<H, W>;
   using SM = FwdSmem<H, W>;
   auto kern = fftmix_tc_fwd_kernel<H, W>;
-  static bool configured = false;
-  if (!configured) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kBytes) != cudaSuccess)
-      return fail(SPECTRE_E_CUDA, "cudaFuncSetAttribute(tc fwd): %s", cudaGetErrorString(cudaGetLastError()));
-    configured = true;
-  }
+  if (ensure_dynamic_smem(reinterpret_cast<const void*>(kern), SM::kBytes) != cudaSuccess)
+    return fail(SPECTRE_E_CUDA, "cudaFuncSetAttribute(tc fwd): %s", cudaGetErrorString(cudaGetLastError()));
   CUtensorMap tmx, tmy;
   if (int rc = make_token_map(&tmx, x, B, C::HW, C::HW + cls, E, cls)) return rc;
   if (int rc = make_token_map(&tmy, y, B, C::HW, C::HW + cls, E, cls)) return rc;
@@ -1209,12 +1205,8 @@ static int bwd_launch(const void* dy, const void* x, const float* filt, void* dx
   using C = Cfg<H, W>;
   using SM = BwdSmem<H, W>;
   auto kern = fftmix_tc_bwd_kernel<H, W>;
-  static bool configured = false;
-  if (!configured) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::kBytes) != cudaSuccess)
-      return fail(SPECTRE_E_CUDA, "cudaFuncSetAttribute(tc bwd): %s", cudaGetErrorString(cudaGetLastError()));
-    configured = true;
-  }
+  if (ensure_dynamic_smem(reinterpret_cast<const void*>(kern), SM::kBytes) != cudaSuccess)
+    return fail(SPECTRE_E_CUDA, "cudaFuncSetAttribute(tc bwd): %s", cudaGetErrorString(cudaGetLastError()));
   BwdParams p;
   plan_bwd_grid(B, E, &p.nblk, &p.pair_stride);
   const size_t slab_floats = static_cast<size_t>(H) * C::WH * E * 2;

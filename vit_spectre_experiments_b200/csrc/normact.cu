@@ -70,6 +70,7 @@ __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint
                ::"r"(ptx::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(ptx::smem_u32(bar)) : "memory");
 }
 constexpr int kMaxStages = 4;
+constexpr int kMaxSmem = 200 * 1024;   // opt-in dynamic shared memory of every kernel here
 
 __device__ __forceinline__ void ld8(const float* p, float (&v)[8]) {
   const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
@@ -785,10 +786,6 @@ struct KernelTable {
     fill_row<__nv_bfloat16, 2, 1>(fwd[1][1][1], bwd[1][1][1], Seq{});
     fill_row<__nv_bfloat16, 3, 0>(fwd[1][2][0], bwd[1][2][0], Seq{});
     fill_row<__nv_bfloat16, 3, 1>(fwd[1][2][1], bwd[1][2][1], Seq{});
-    for (auto& t : fwd) for (auto& v : t) for (auto& w : v) for (KernelFn f : w)
-      cudaFuncSetAttribute(reinterpret_cast<const void*>(f), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    for (auto& t : bwd) for (auto& v : t) for (auto& w : v) for (KernelFn f : w)
-      if (f) cudaFuncSetAttribute(reinterpret_cast<const void*>(f), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   }
 };
 static const KernelTable& table() {
@@ -813,12 +810,26 @@ int spectre_norm_act_fwd(const spectre_norm_act_t* d, void* stream) {
   a.tpr = sh.tpr; a.rpc = sh.rpc; a.stages = sh.stages; a.stage_bytes = sh.stage_bytes;
   const int grid = grid_for(a.rows, sh), block = sh.tpr * sh.rpc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  table().fwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
+  const KernelFn kern = table().fwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode];
+  if (sh.smem > kMaxSmem || ensure_dynamic_smem(reinterpret_cast<const void*>(kern), kMaxSmem) != cudaSuccess)
+    return fail(SPECTRE_E_SHAPE, "spectre_norm_act_fwd: N=%d Ns=%d needs %zu B of shared memory (limit %d)", a.N, a.Ns, sh.smem, kMaxSmem);
+  kern<<<grid, block, sh.smem, st>>>(a);
   last_launch_count() = 1;
   const cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "norm_act_fwd launch: %s", cudaGetErrorString(err));
   last_error().clear();
   return SPECTRE_OK;
+}
+
+int spectre_norm_act_supported(int N, int Ns, int act_dtype) {
+  if (N < 8 || (N % 8) || N > 4096 || Ns < 8 || (Ns % 8) || Ns > 16384) return 0;
+  if (act_dtype != SPECTRE_DTYPE_F32 && act_dtype != SPECTRE_DTYPE_BF16) return 0;
+  const int elem = act_dtype == SPECTRE_DTYPE_BF16 ? 2 : 4;
+  const bool general = pick_skip(N, Ns, true) == kSkipGeneral;
+  // the widest launches of each direction: forward with in1 and a skip, backward with in1, dout2 and column sums
+  const Shape f = launch_shape(N, Ns, true, true, elem, false, false, 2, general);
+  const Shape b = launch_shape(N, Ns, true, false, elem, true, true, 3, general);
+  return f.smem <= static_cast<size_t>(kMaxSmem) && b.smem <= static_cast<size_t>(kMaxSmem) ? 1 : 0;
 }
 
 // upper bound over element types / optional operands (the query has no such arguments)
@@ -847,7 +858,10 @@ int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
     return fail(SPECTRE_E_WORKSPACE, "spectre_norm_act_bwd: workspace %zu B < required %zu B", d->workspace_bytes,
                 static_cast<size_t>(grid) * a.nacc * a.N * sizeof(float));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  table().bwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode]<<<grid, block, sh.smem, st>>>(a);
+  const KernelFn kern = table().bwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode];
+  if (sh.smem > kMaxSmem || ensure_dynamic_smem(reinterpret_cast<const void*>(kern), kMaxSmem) != cudaSuccess)
+    return fail(SPECTRE_E_SHAPE, "spectre_norm_act_bwd: N=%d Ns=%d needs %zu B of shared memory (limit %d)", a.N, a.Ns, sh.smem, kMaxSmem);
+  kern<<<grid, block, sh.smem, st>>>(a);
   int launches = 1;
   reduce_gamma_beta_kernel<<<(a.nacc * a.N + 7) / 8, 256, 0, st>>>(a.part, d->dgamma, d->dbeta, d->dcolsum, a.N, a.nacc, grid);
   ++launches;

@@ -28,6 +28,22 @@ def _resolve_grid(token_dim: int, grid, has_cls: bool):
     return H, W
 
 
+def _require_kernel(kind: str, H: int, W: int, E: int) -> None:
+    """Fail at construction, not at the first forward, when no kernel is compiled for the grid (there is no
+    fallback to torch.fft).  Skipped when the library has not been built yet: the forward raises then anyway."""
+    if E % 2:
+        raise ValueError(f"{kind} mixer: embed_dim must be even, got {E}")
+    try:
+        from . import _lib
+
+        lib = _lib.load()
+    except (RuntimeError, OSError):
+        return
+    if kind == "fft" and lib.spectre_fftmix_supported(H, W) != 1:
+        raise ValueError(f"SpectralFilterMix: no CUDA kernel is compiled for a {H}x{W} grid "
+                         "(see fftmix_supported in csrc/fftmix.cu for the list)")
+
+
 class _Fp32ParamMixin:
     """Learned spectral parameters stay float32 under ``.half()`` / ``.bfloat16()`` / ``.to(dtype)``:
     the kernels take fp32 parameters and emit fp32 parameter gradients whatever the activation dtype."""
@@ -44,14 +60,24 @@ class _Fp32ParamMixin:
         return self
 
     @staticmethod
-    def _activation(x: torch.Tensor) -> torch.Tensor:
-        if torch.is_autocast_enabled():
-            dt = torch.get_autocast_dtype("cuda")
-            if dt != torch.bfloat16:
-                raise RuntimeError(f"spectral mixers support autocast to bfloat16 only (got {dt})")
-            if x.dtype != dt:
-                x = x.to(dt)
-        return x
+    def _activation(x: torch.Tensor):
+        """Dtype the kernels run in, following what ``torch.fft`` does in the same place.
+
+        * bf16 autocast (the build's training stream): bf16 kernels, bf16 result;
+        * any other autocast dtype -- the reference trains under ``torch.autocast(dtype=torch.float16)`` + ``GradScaler``
+          (``spectre_vit/repl/train.py:205,219``): ``torch.fft`` is on autocast's fp32 list there, so ``x`` is up-cast
+          to float32, the fp32 kernels run and the result stays float32;
+        * no autocast: fp32 / bf16 tensors run as they are; a float16 / float64 tensor (``model.half()``) runs the fp32
+          kernels and the result is cast back to its dtype.
+        Returns ``(x_for_the_kernel, dtype_of_the_result)``."""
+        if torch.is_autocast_enabled(x.device.type):
+            dt = torch.get_autocast_dtype(x.device.type)
+            if dt == torch.bfloat16:
+                return (x if x.dtype == dt else x.to(dt)), dt
+            return x.float(), torch.float32
+        if x.dtype in (torch.float32, torch.bfloat16):
+            return x, x.dtype
+        return x.float(), x.dtype
 
 
 class SpectralFilterMix(_Fp32ParamMixin, nn.Module):
@@ -74,12 +100,15 @@ class SpectralFilterMix(_Fp32ParamMixin, nn.Module):
         self.has_cls = bool(has_cls)
         self.grid = _resolve_grid(token_dim, grid, self.has_cls)
         H, W = self.grid
+        _require_kernel("fft", H, W, embed_dim)
         f = torch.zeros(H, W // 2 + 1, embed_dim, 2)
         f[..., 0] = 1.0
         self.filter = nn.Parameter(f + init_std * torch.randn_like(f))
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return fft_mix(self._activation(x), self.filter, self.grid, self.has_cls)
+        xa, out_dt = self._activation(x)
+        y = fft_mix(xa, self.filter, self.grid, self.has_cls)
+        return y if y.dtype == out_dt else y.to(out_dt)
 
     def extra_repr(self) -> str:
         return f"embed_dim={self.embed_dim}, grid={self.grid}, has_cls={self.has_cls}"
@@ -112,12 +141,17 @@ class HaarDWTMix(_Fp32ParamMixin, nn.Module):
             # J levels (the reference call site uses J=3): coefficients in place on the token lattice, [H, W, E]
             if self.levels < 1 or H % (1 << self.levels) or W % (1 << self.levels):
                 raise ValueError(f"levels={levels} needs H and W to be multiples of 2^levels, got {H}x{W}")
+            if H * W > 256 or embed_dim % 4:
+                raise ValueError(f"multi-level Haar kernel: needs H*W <= 256 and embed_dim % 4 == 0, got {H}x{W}, E={embed_dim}")
             self.weight = nn.Parameter(1.0 + init_std * torch.randn(H, W, embed_dim))
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        xa, out_dt = self._activation(x)
         if self.levels == 1:
-            return dwt_mix(self._activation(x), self.weight, self.grid, self.has_cls)
-        return dwt_mix_ml(self._activation(x), self.weight, self.grid, self.has_cls, self.levels)
+            y = dwt_mix(xa, self.weight, self.grid, self.has_cls)
+        else:
+            y = dwt_mix_ml(xa, self.weight, self.grid, self.has_cls, self.levels)
+        return y if y.dtype == out_dt else y.to(out_dt)
 
     def extra_repr(self) -> str:
         return f"embed_dim={self.embed_dim}, grid={self.grid}, has_cls={self.has_cls}"

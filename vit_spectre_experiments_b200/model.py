@@ -76,13 +76,14 @@ class MHPermutMix(nn.Module):
 
     def _inverse(self) -> torch.Tensor:
         """Inverse permutations for the CUDA backward (plain attribute: not part of ``state_dict``)."""
-        inv = getattr(self, "_inv", None)
-        if inv is None or inv.device != self.perms.device or getattr(self, "_inv_of", None) is not self.perms:
+        # keyed on the buffer's storage, VERSION and device: ``load_state_dict`` copies into ``perms`` in place
+        # (same tensor object, bumped version), ``.to(device)`` replaces it
+        key = (self.perms.data_ptr(), self.perms._version, self.perms.device)
+        if getattr(self, "_inv_key", None) != key:
             from .functional import inverse_permutations
 
-            inv = inverse_permutations(self.perms)
-            self._inv, self._inv_of = inv, self.perms
-        return inv
+            self._inv, self._inv_key = inverse_permutations(self.perms), key
+        return self._inv
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         batch = x.shape[0]
@@ -130,15 +131,31 @@ class SpectreEncoderLayer(nn.Module):
         self.dropout2 = nn.Dropout(dropout)
         self.activation = getattr(F, activation) if isinstance(activation, str) else activation
         self.fused = _FUSED_DEFAULT if fused is None else bool(fused)
-        self._fusable = d_model % 8 == 0 and dim_feedforward % 8 == 0
+        self._fusable = None   # resolved on first CUDA use: do the fused row-wise kernels take these widths?
 
     def _ff_block(self, x: torch.Tensor) -> torch.Tensor:
         return self.dropout2(self.linear3(self.dropout1(self.linear1(x))))
 
+    def _widths_supported(self) -> bool:
+        """``spectre_norm_act_supported`` for the three tails of the layer (widths beyond the kernels' limits keep the
+        torch composition instead of failing mid-forward)."""
+        if self._fusable is None:
+            from . import _lib
+
+            lib = _lib.load()
+            E, hid = self.norm1.normalized_shape[0], self.linear1.out_channels
+            self._fusable = all(lib.spectre_norm_act_supported(n, ns, dt) == 1
+                                for dt in (0, 1) for n, ns in ((E, E), (hid, E), (E, hid)))
+        return self._fusable
+
     def use_fused(self, x: torch.Tensor) -> bool:
-        if not (self.fused and self._fusable and x.is_cuda and x.dtype in (torch.float32, torch.bfloat16)):
+        if not (self.fused and x.is_cuda and x.dtype in (torch.float32, torch.bfloat16)):
             return False
-        return not torch.is_autocast_enabled() or torch.get_autocast_dtype("cuda") == torch.bfloat16
+        if torch.is_autocast_enabled() and torch.get_autocast_dtype("cuda") != torch.bfloat16:
+            # the reference's fp16 autocast (repl/train.py:219): the stock composition runs around the CUDA mixer,
+            # which follows torch.fft's autocast rule (fp32 in, fp32 out)
+            return False
+        return self._widths_supported()
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.use_fused(x):
