@@ -260,8 +260,10 @@ def main():
         # mean_ms = the main kernel of the call; mean_call_ms = the whole C-ABI call (a backward mixer call ends
         # with a few-microsecond reduction kernel of the per-slab parameter gradients)
         for name, (n, call_ms, meta, mean_ms) in ksum.items():
-            if len(meta) != 5:      # row-wise tails (norm_act_*): rows, N, element size -- time only
-                kernels[name] = {"launches": n, "mean_ms": round(mean_ms, 4)}
+            if len(meta) != 5:      # row-wise tails (norm_act_*:N:Ns:act:in1): rows, N, element size, algorithmic bytes
+                nb = meta[3]
+                kernels[name] = {"launches": n, "mean_ms": round(mean_ms, 4), "algo_bytes": nb,
+                                 "GBps": round(nb / mean_ms / 1e6, 1), "frac": round(nb / mean_ms / 1e6 / peaks["hbm_gbs"], 4)}
                 continue
             Bk, Hk, Wk, Ek, sz = meta
             nbytes = (3 if name.endswith("bwd") else 2) * Bk * T * Ek * sz + (2 if name.endswith("bwd") else 1) * F

@@ -111,6 +111,12 @@ typedef struct spectre_norm_act_t {
   float eps; float drop_p; unsigned long long seed;
   int reverse /* 0: rows swept first to last; 1: last to first (same result; lets a caller that knows which end of
                  the operands its producer left hot in L2 start there) */;
+  /* Optional pooled copy of the result: out_pool[r, i] = mean(out[r, i*pool_k .. (i+1)*pool_k)), pool_k in {2, 4, 8},
+   * N a multiple of 8*pool_k -- what AdaptiveAvgPool1d(N / pool_k) of `out` would give, i.e. the skip operand of the
+   * NEXT SpectreLinear when it narrows N -> N / pool_k (layers.py:92,101), emitted here so that consumer reads
+   * N / pool_k columns per row instead of N.  Backward: d_out_pool [rows, N / pool_k] is the gradient that arrived
+   * through out_pool; it is added as d_out_pool[r, j / pool_k] / pool_k to dout[r, j].  NULL = unused. */
+  void* out_pool; const void* d_out_pool; int pool_k;
 } spectre_norm_act_t;
 
 int spectre_norm_act_fwd(const spectre_norm_act_t* desc, void* stream);

@@ -110,62 +110,68 @@ def main():
         norm_act_bench(args, dev, flush)
 
 
-# the four row-wise tails of one C4 encoder layer (rows = 256 * 197) + C3 widths
-NA_SHAPES = [
-    # name, rows, N, Ns, has_in1, act, drop_p, dtype
-    ("C4 LN1(mix)+x N384", 256 * 197, 384, 384, False, "none", 0.0, torch.bfloat16),
-    ("C4 GELU(LN(h1))+up N1536", 256 * 197, 1536, 384, False, "gelu", 0.001, torch.bfloat16),
-    ("C4 GELU(LN(h2))+down N384", 256 * 197, 384, 1536, False, "gelu", 0.001, torch.bfloat16),
-    ("C4 LN2(x1+ff) N384", 256 * 197, 384, None, True, "none", 0.0, torch.bfloat16),
-    ("C4 GELU(LN(h1))+up N1536 f32", 256 * 197, 1536, 384, False, "gelu", 0.001, torch.float32),
-    ("C4 bench B2048 LN1(mix)+x N384", 2048 * 197, 384, 384, False, "none", 0.0, torch.bfloat16),
-    ("C4 bench B2048 GELU(LN(h1))+up N1536", 2048 * 197, 1536, 384, False, "gelu", 0.001, torch.bfloat16),
-    ("C4 bench B2048 GELU(LN(h2))+down N384", 2048 * 197, 384, 1536, False, "gelu", 0.001, torch.bfloat16),
-    ("C4 bench B2048 LN2(x1+ff) N384", 2048 * 197, 384, None, True, "none", 0.0, torch.bfloat16),
-    ("C5 B512 GELU(LN(h1))+up N3072", 512 * 197, 3072, 768, False, "gelu", 0.001, torch.bfloat16),
-    ("C5 B512 GELU(LN(h2))+down N768", 512 * 197, 768, 3072, False, "gelu", 0.001, torch.bfloat16),
-    ("C3 GELU(LN(h1))+general 512->768", 1024 * 65, 768, 512, False, "gelu", 0.001, torch.bfloat16),
-    ("C3 GELU(LN(h2))+general 768->512", 1024 * 65, 512, 768, False, "gelu", 0.001, torch.bfloat16),
-    ("C2 GELU(LN(h1))+general 48->256 f32", 4096 * 50, 256, 48, False, "gelu", 0.001, torch.float32),
-    ("C2 GELU(LN(h2))+general 256->48 f32", 4096 * 50, 48, 256, False, "gelu", 0.001, torch.float32),
-]
+# the row-wise tails of one encoder layer as fused.encoder_layer calls them (bf16 stream unless noted)
+#   name, rows, N, Ns (skip width, 0 = none), in1, act, drop_p, dtype, pool_k (fwd out_pool / bwd d_out_pool), dout2, colsum
+def _layer_shapes(tag, rows, E, hid, dt=torch.bfloat16):
+    return [
+        (f"{tag} LN1(mix)+x N{E}", rows, E, E, False, 0, 0.0, dt, 0, True, False),
+        (f"{tag} GELU(LN(h1))+up+pool N{hid}", rows, hid, E, False, 1, 0.001, dt, hid // E, False, True),
+        (f"{tag} GELU(LN(h2))+pooled N{E}", rows, E, E, False, 1, 0.001, dt, 0, False, True),
+        (f"{tag} LN2(x1+ff) N{E}", rows, E, 0, True, 0, 0.0, dt, 0, True, False),
+    ]
+
+
+NA_SHAPES = (
+    _layer_shapes("C4 B256", 256 * 197, 384, 1536)
+    + _layer_shapes("C4 B2048", 2048 * 197, 384, 1536)
+    + _layer_shapes("C5 B512", 512 * 197, 768, 3072)
+    + [
+        ("C4 B2048 GELU(LN(h2))+down N384 (r1 layout)", 2048 * 197, 384, 1536, False, 1, 0.001, torch.bfloat16, 0, False, True),
+        ("C4 B256 GELU(LN(h1))+up N1536 f32", 256 * 197, 1536, 384, False, 1, 0.001, torch.float32, 0, False, True),
+        ("C3 GELU(LN(h1))+general 512->768", 1024 * 65, 768, 512, False, 1, 0.001, torch.bfloat16, 0, False, True),
+        ("C3 GELU(LN(h2))+general 768->512", 1024 * 65, 512, 768, False, 1, 0.001, torch.bfloat16, 0, False, True),
+        ("C3 LN1(mix)+x N512", 1024 * 65, 512, 512, False, 0, 0.0, torch.bfloat16, 0, True, False),
+        ("C2 GELU(LN(h1))+general 48->256 f32", 4096 * 50, 256, 48, False, 1, 0.001, torch.float32, 0, False, True),
+        ("C2 GELU(LN(h2))+general 256->48 f32", 4096 * 50, 48, 256, False, 1, 0.001, torch.float32, 0, False, True),
+    ]
+)
 
 
 def norm_act_bench(args, dev, flush):
-    from vit_spectre_experiments_b200.fused import norm_act
+    from vit_spectre_experiments_b200.functional import TIMER
+    from vit_spectre_experiments_b200.fused import na_bwd, na_fwd
 
-    for name, rows, N, Ns, has_in1, act, p, dt in NA_SHAPES:
+    for name, rows, N, Ns, has_in1, act, p, dt, pool_k, has_d2, colsum in NA_SHAPES:
         if args.match and not re.search(args.match, name):
             continue
-        s = 4 if dt == torch.float32 else 2
-        in0 = torch.randn(rows, N, device=dev).to(dt).requires_grad_(True)
-        in1 = torch.randn(rows, N, device=dev).to(dt).requires_grad_(True) if has_in1 else None
-        skip = torch.randn(rows, Ns, device=dev).to(dt).requires_grad_(True) if Ns else None
-        gamma = torch.ones(N, device=dev, requires_grad=True)
-        beta = torch.zeros(N, device=dev, requires_grad=True)
-        dout = torch.randn(rows, N, device=dev).to(dt)
-        out = [None]
+        rnd = lambda *s: torch.randn(*s, device=dev).to(dt)   # noqa: E731
+        in0 = rnd(rows, N)
+        in1 = rnd(rows, N) if has_in1 else None
+        skip = rnd(rows, Ns) if Ns else None
+        gamma, beta = torch.ones(N, device=dev), torch.zeros(N, device=dev)
+        dout = rnd(rows, N)
+        dout2 = rnd(rows, N) if has_d2 else None
+        dpool = rnd(rows, N // pool_k) if pool_k else None
+        res = na_fwd(in0, gamma, beta, in1, skip, act=act, drop_p=p, seed=11, pool_k=pool_k)
+        mean, rstd = res[1], res[2]
 
         def fwd():
-            out[0] = norm_act(in0, gamma, beta, in1=in1, skip=skip, act=act, drop_p=p, seed=11)
+            na_fwd(in0, gamma, beta, in1, skip, act=act, drop_p=p, seed=11, pool_k=pool_k)
 
         def bwd():
-            torch.autograd.grad(out[0], [t for t in (in0, in1, skip, gamma, beta) if t is not None], dout,
-                                retain_graph=True)
+            na_bwd(dout, in0, gamma, beta, mean, rstd, in1, (rows, Ns) if Ns else None, act=act, drop_p=p, seed=11,
+                   dout2=dout2, colsum=colsum, d_out_pool=dpool, pool_k=pool_k)
 
-        nin = rows * N * s * (2 if has_in1 else 1) + (rows * Ns * s if Ns else 0)
-        fb = nin + rows * N * s                                   # inputs + out
-        bb = rows * N * s * (3 if not has_in1 else 4) + (rows * Ns * s if Ns else 0)   # dout, in0(+in1), d_in0, d_skip
-        from vit_spectre_experiments_b200.functional import TIMER
-        for which, fn, nbytes in (("fwd", fwd, fb), ("bwd", bwd, bb)):
-            # time the C-ABI call only (CUDA events around it), not the autograd / allocator plumbing
+        for which, fn in (("fwd", fwd), ("bwd", bwd)):
             ts = []
+            nbytes = 0
             for it in range(args.iters + 3):
                 flush.zero_()
                 TIMER.reset(); TIMER.enabled = True
                 fn()
                 TIMER.enabled = False
-                (n, ms, _, _), = TIMER.summary().values()
+                (n, ms, meta, main_ms), = TIMER.summary().values()
+                nbytes = meta[3]
                 if it >= 3:
                     ts.append(ms)
             ts.sort()
@@ -175,6 +181,8 @@ def norm_act_bench(args, dev, flush):
                 "algo_MB": round(nbytes / 1e6, 2), "GBps_median": round(nbytes / med / 1e6, 1),
                 "frac_of_measured_peak": round(nbytes / med / 1e6 / PEAK, 3),
             }), flush=True)
+        del in0, in1, skip, dout, dout2, dpool, res
+        torch.cuda.empty_cache()
 
 
 if __name__ == "__main__":

@@ -160,5 +160,6 @@ def test_norm_act_bench_rows(cuda_device, rows, N, Ns, has_in1, act):
         assert torch.equal(leaves[3].grad, leaves[0].grad)
     # fp32 parameter gradients summed over 4e5 bf16 rows: the rounding of d_in0's inputs is shared with the reference,
     # what is left is fp32 summation order
-    assert (leaves[1].grad.double() - dg).abs().max().item() <= 2e-4 * dg.abs().max().item()
-    assert (leaves[2].grad.double() - db).abs().max().item() <= 2e-4 * db.abs().max().item()
+    ptol = 2e-3 if act == "gelu" else 2e-4     # bf16 stream: Phi through MUFU.TANH (relative error 2^-11)
+    assert (leaves[1].grad.double() - dg).abs().max().item() <= ptol * dg.abs().max().item()
+    assert (leaves[2].grad.double() - db).abs().max().item() <= ptol * db.abs().max().item()

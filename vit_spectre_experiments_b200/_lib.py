@@ -48,6 +48,7 @@ class NormActDesc(ctypes.Structure):
         ("workspace_bytes", ctypes.c_size_t), ("rows", ctypes.c_longlong), ("N", ctypes.c_int), ("Ns", ctypes.c_int),
         ("act_dtype", ctypes.c_int), ("act", ctypes.c_int), ("eps", ctypes.c_float), ("drop_p", ctypes.c_float),
         ("seed", ctypes.c_ulonglong), ("reverse", ctypes.c_int),
+        ("out_pool", ctypes.c_void_p), ("d_out_pool", ctypes.c_void_p), ("pool_k", ctypes.c_int),
     ]
 
 

@@ -29,48 +29,13 @@
 // one odd multiply of a per-vector hash per element for the mask, pooling ratios resolved at compile time
 // (general widths: window tables built once per CTA in shared memory, transpose fused into the backward).
 #include <cstdarg>
+#include <type_traits>
 #include <utility>
 
-#include "common.cuh"
-#include "sm100_ptx.cuh"
+#include "normact_common.cuh"
 
 namespace sb200 {
 namespace na {
-
-// skip variants; every kernel instantiation carries exactly one (lean inner loops, small code)
-enum : int { kSkipNone = 0, kSkipIdentity = 1, kSkipUp2 = 2, kSkipUp4 = 3, kSkipUp8 = 4, kSkipDown2 = 5, kSkipDown4 = 6,
-             kSkipDown8 = 7, kSkipGeneral = 8, kSkipModes = 9 };
-constexpr int up_k(int mode) { return mode == kSkipUp2 ? 2 : mode == kSkipUp4 ? 4 : mode == kSkipUp8 ? 8 : 0; }
-constexpr int down_k(int mode) { return mode == kSkipDown2 ? 2 : mode == kSkipDown4 ? 4 : mode == kSkipDown8 ? 8 : 0; }
-
-struct Args {
-  const void* in0; const void* in1; const float* gamma; const float* beta; const void* skip;
-  void* out; float* mean; float* rstd;
-  const void* dout; const void* dout2;   // upstream gradient (+ optional second addend)
-  void* d_in0; void* d_skip; float* part;   // part: [grid][nacc][N] partials: dgamma, dbeta (, column sums of d_in0)
-  int nacc;
-  long long rows; int N; int Ns; int act; int skip_mode;
-  int tpr; int rpc;                                                 // threads per row, rows per CTA
-  int stages; int stage_bytes;                                      // shared-memory ring of input row groups
-  float eps; float drop_p; unsigned seed_lo; unsigned seed_hi;
-  int reverse;   // sweep the row groups from the last to the first (the caller knows where the producer left L2 hot)
-};
-
-// ------------------------------------------------------------------ typed vector I/O
-__device__ __forceinline__ float bf_lo(unsigned u) { return __uint_as_float(u << 16); }
-__device__ __forceinline__ float bf_hi(unsigned u) { return __uint_as_float(u & 0xffff0000u); }
-__device__ __forceinline__ unsigned bf_pack(float lo, float hi) {
-  const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<const unsigned*>(&h);
-}
-
-// 1-D bulk async copy global -> shared (16-byte aligned, size a multiple of 16), completion on an mbarrier
-__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(ptx::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(ptx::smem_u32(bar)) : "memory");
-}
-constexpr int kMaxStages = 4;
-constexpr int kMaxSmem = 200 * 1024;   // opt-in dynamic shared memory of every kernel here
 
 __device__ __forceinline__ void ld8(const float* p, float (&v)[8]) {
   const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
@@ -118,62 +83,6 @@ __device__ __forceinline__ float ld1(const float* p) { return *p; }   // also re
 __device__ __forceinline__ float ld1(const __nv_bfloat16* p) { return __bfloat162float(*p); }
 __device__ __forceinline__ void st1(float* p, float v) { *p = v; }
 __device__ __forceinline__ void st1(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
-
-// ------------------------------------------------------------------ GELU (erf form, nn.GELU() of layers.py:89)
-// erf(|u|) = 1 - (a1 t + ... + a5 t^5) exp(-u^2),  t = 1 / (1 + p |u|)      (Abramowitz & Stegun 7.1.26)
-// returns Phi(x) = 0.5 (1 + erf(x / sqrt 2)) and, through *gauss, exp(-x^2 / 2)
-__device__ __forceinline__ float rcp_approx(float x) {
-  float r;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-  return r;
-}
-__device__ __forceinline__ float ex2_approx(float x) {
-  float r;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-  return r;
-}
-__device__ __forceinline__ float norm_cdf(float x, float* gauss) {
-  const float t = rcp_approx(fmaf(0.3275911f * 0.70710678118654752f, fabsf(x), 1.0f));
-  const float e = ex2_approx(x * x * -0.72134752044448170f);     // exp(-x^2 / 2)
-  float poly = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);   // coefficients pre-halved
-  poly = fmaf(poly, t, 0.5f * 1.421413741f);
-  poly = fmaf(poly, t, 0.5f * -0.284496736f);
-  poly = fmaf(poly, t, 0.5f * 0.254829592f);
-  const float half_tail = poly * (t * e);             // 0.5 * erfc(|x| / sqrt 2)
-  *gauss = e;
-  return x >= 0.f ? 1.0f - half_tail : half_tail;
-}
-__device__ __forceinline__ float gelu(float x) {
-  float g;
-  return x * norm_cdf(x, &g);
-}
-__device__ __forceinline__ float gelu_grad(float x) {
-  float g;
-  const float cdf = norm_cdf(x, &g);
-  return fmaf(x * 0.39894228040143268f, g, cdf);
-}
-
-// counter-based dropout.  A vector of 8 columns shares one well-mixed 32-bit word (lowbias32 of the vector
-// index under the row seed); element e takes one more odd multiply of it, and is kept iff the
-// result >= drop_p * 2^32.  Forward and backward both go through keep_e().
-__device__ __forceinline__ unsigned vec_hash(unsigned seed, unsigned vec) {
-  unsigned x = vec ^ seed;
-  x ^= x >> 16; x *= 0x7feb352du;
-  x ^= x >> 15; x *= 0x846ca68bu;
-  x ^= x >> 16;
-  return x;
-}
-__device__ __forceinline__ bool keep_e(unsigned vh, int e, unsigned thresh) {
-  constexpr unsigned kMul[8] = {0x9E3779B1u, 0x85EBCA77u, 0xC2B2AE3Du, 0x27D4EB2Fu, 0x165667B1u, 0xD3A2646Du, 0xFD7046C5u, 0xB55A4F09u};
-  return vh * kMul[e] >= thresh;   // the comparison is decided by the high bits: no further mixing needed
-}
-// seed of a row: folds the high bits of the 64-bit seed and the row index so idx can stay 32-bit (column)
-__device__ __forceinline__ unsigned row_seed(const Args& a, long long row) {
-  unsigned long long z = (static_cast<unsigned long long>(a.seed_hi) << 32 | a.seed_lo) + static_cast<unsigned long long>(row) * 0x9E3779B97F4A7C15ull;
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z ^= z >> 27;
-  return static_cast<unsigned>(z >> 16);
-}
 
 // sum over the threads of one row of NV values.  One warp per row: shuffles only.  Several warps per row:
 // one CTA-wide barrier (every row group of the CTA executes the same trip count); `slot` alternates so
@@ -301,6 +210,39 @@ __device__ __forceinline__ void skip_down_bwd(T* drow, int j0, const float (&d)[
   }
 }
 
+// second output: pooled[j0 / K + i] = mean(o[i K .. (i + 1) K)), K in {2, 4, 8}; and its transpose in the backward
+template <class T, int K>
+__device__ __forceinline__ void pool_store_k(T* prow, int j0, const float (&o)[8]) {
+  float s[8 / K];
+#pragma unroll
+  for (int i = 0; i < 8 / K; ++i) {
+    float acc = 0.f;
+#pragma unroll
+    for (int r = 0; r < K; ++r) acc += o[i * K + r];
+    s[i] = acc * (1.0f / K);
+  }
+  stn<8 / K>(prow + j0 / K, s);
+}
+template <class T>
+__device__ __forceinline__ void pool_store(T* prow, int j0, int k, const float (&o)[8]) {
+  if (k == 4) pool_store_k<T, 4>(prow, j0, o);
+  else if (k == 2) pool_store_k<T, 2>(prow, j0, o);
+  else pool_store_k<T, 8>(prow, j0, o);
+}
+template <class T, int K>
+__device__ __forceinline__ void pool_grad_add_k(const T* prow, int j0, float (&d)[8]) {
+  float s[8 / K];
+  ldn<8 / K>(prow + j0 / K, s);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) d[e] = fmaf(s[e / K], 1.0f / K, d[e]);
+}
+template <class T>
+__device__ __forceinline__ void pool_grad_add(const T* prow, int j0, int k, float (&d)[8]) {
+  if (k == 4) pool_grad_add_k<T, 4>(prow, j0, d);
+  else if (k == 2) pool_grad_add_k<T, 2>(prow, j0, d);
+  else pool_grad_add_k<T, 8>(prow, j0, d);
+}
+
 // ------------------------------------------------------------------ forward
 template <class T, int VPT, int MODE, int ACT>
 __global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(const Args a) {
@@ -312,8 +254,8 @@ __global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(con
   const int nvec = a.N >> 3, S = a.stages;
   const float inv_n = 1.0f / static_cast<float>(a.N);
   const bool drop = a.drop_p > 0.f;
-  const unsigned thresh = drop ? static_cast<unsigned>(fminf(a.drop_p, 0.999999f) * 4294967296.0f) : 0u;
-  const float keep_scale = drop ? 1.0f / (1.0f - a.drop_p) : 1.0f;
+  const float keep_scale = a.keep_scale;
+  constexpr bool kFastGelu = std::is_same<T, __nv_bfloat16>::value;   // bf16 stream: tanh-form Phi (normact_common.cuh)
   const long long groups = (a.rows + a.rpc - 1) / a.rpc;
   const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
   auto group_of = [&](int it) {   // row group of iteration it: ascending, or descending from the last group
@@ -408,7 +350,7 @@ __global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(con
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           const float u = fmaf(fmaf(z[i][e], rstd, shift), g[e], b[e]);
-          o[e] = ACT ? gelu(u) : u;
+          o[e] = ACT ? gelu<kFastGelu>(u) : u;
         }
         if constexpr (MODE == kSkipIdentity) {
           float sk[8];
@@ -423,11 +365,12 @@ __global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(con
           skip_general_add<T>(srow, win, j0, a.N >= a.Ns, o);
         }
         if (drop) {
-          const unsigned vh = vec_hash(rseed, static_cast<unsigned>(v));
+          const unsigned dm = drop_mask8(a, rseed, static_cast<unsigned>(v));
 #pragma unroll
-          for (int e = 0; e < 8; ++e) o[e] = keep_e(vh, e, thresh) ? o[e] * keep_scale : 0.f;
+          for (int e = 0; e < 8; ++e) o[e] = (dm >> e & 1u) ? 0.f : o[e] * keep_scale;
         }
         st8(static_cast<T*>(a.out) + row * a.N + j0, o);
+        if (a.out_pool) pool_store<T>(static_cast<T*>(a.out_pool) + row * (a.N / a.pool_k), j0, a.pool_k, o);
       }
     }
     __syncthreads();   // every thread is done with this stage: the producer may refill it
@@ -458,8 +401,8 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   float* dn = reinterpret_cast<float*>(cov + a.Ns) + rg * a.N;
   const float inv_n = 1.0f / static_cast<float>(a.N);
   const bool drop = a.drop_p > 0.f;
-  const unsigned thresh = drop ? static_cast<unsigned>(fminf(a.drop_p, 0.999999f) * 4294967296.0f) : 0u;
-  const float keep_scale = drop ? 1.0f / (1.0f - a.drop_p) : 1.0f;
+  const float keep_scale = a.keep_scale;
+  constexpr bool kFastGelu = std::is_same<T, __nv_bfloat16>::value;   // bf16 stream: tanh-form Phi (normact_common.cuh)
   const long long groups = (a.rows + a.rpc - 1) / a.rpc;
   const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
   auto group_of = [&](int it) {
@@ -549,10 +492,11 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) d[e] += w[e];
       }
+      if (a.d_out_pool) pool_grad_add<T>(static_cast<const T*>(a.d_out_pool) + row * (a.N / a.pool_k), j0, a.pool_k, d);
       if (drop) {
-        const unsigned vh = vec_hash(rseed, static_cast<unsigned>(v));
+        const unsigned dm = drop_mask8(a, rseed, static_cast<unsigned>(v));
 #pragma unroll
-        for (int e = 0; e < 8; ++e) d[e] = keep_e(vh, e, thresh) ? d[e] * keep_scale : 0.f;
+        for (int e = 0; e < 8; ++e) d[e] = (dm >> e & 1u) ? 0.f : d[e] * keep_scale;
       }
       // ---- skip path: transpose of the pooling
       if constexpr (MODE == kSkipIdentity) {
@@ -579,7 +523,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
       for (int e = 0; e < 8; ++e) {
         const float x = fmaf(z[e], rstd, shift);
         float g = d[e];
-        if (ACT) g *= gelu_grad(fmaf(x, gam[e], bet[e]));
+        if (ACT) g *= gelu_grad<kFastGelu>(fmaf(x, gam[e], bet[e]));
         db[e] += g;
         dg[e] = fmaf(g, x, dg[e]);
         const float y = g * gam[e];
@@ -666,6 +610,15 @@ __global__ void __launch_bounds__(256) reduce_gamma_beta_kernel(const float* __r
 }
 
 // ------------------------------------------------------------------ host side
+// SB200_NA_FAST=0 keeps the bf16 stream on the generic kernels (A/B measurements); default: normact_fast.cu
+static bool fast_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("SB200_NA_FAST");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 static int pick_skip(int N, int Ns, bool has_skip) {
   if (!has_skip) return kSkipNone;
   if (Ns == N) return kSkipIdentity;
@@ -731,6 +684,13 @@ static int validate(const char* fn, const spectre_norm_act_t* d, bool bwd) {
   for (const void* q : ptrs)
     if (!aligned16(q)) return fail(SPECTRE_E_ALIGN, "%s: pointers must be 16-byte aligned", fn);
   if (!bwd && !d->out) return fail(SPECTRE_E_NULL, "%s: null out", fn);
+  if ((bwd ? d->d_out_pool != nullptr : d->out_pool != nullptr)) {
+    if ((d->pool_k != 2 && d->pool_k != 4 && d->pool_k != 8) || d->N % (8 * d->pool_k))
+      return fail(SPECTRE_E_SHAPE, "%s: pooled output needs pool_k in {2, 4, 8} and N a multiple of 8 * pool_k (pool_k=%d N=%d)",
+                  fn, d->pool_k, d->N);
+    if (!aligned16(d->out_pool) || !aligned16(d->d_out_pool))
+      return fail(SPECTRE_E_ALIGN, "%s: pointers must be 16-byte aligned", fn);
+  }
   if (bwd && (!d->dout || !d->dgamma || !d->dbeta || !d->d_in0)) return fail(SPECTRE_E_NULL, "%s: null gradient pointer", fn);
   return SPECTRE_OK;
 }
@@ -743,7 +703,11 @@ static Args to_args(const spectre_norm_act_t& d, bool bwd) {
   a.nacc = (bwd && d.dcolsum) ? 3 : 2;
   a.part = static_cast<float*>(d.workspace);
   const bool has_skip = bwd ? d.d_skip != nullptr : d.skip != nullptr;
-  a.rows = d.rows; a.N = d.N; a.Ns = has_skip ? d.Ns : d.N; a.act = d.act; a.eps = d.eps; a.drop_p = d.drop_p;
+  a.out_pool = bwd ? nullptr : d.out_pool;
+  a.d_out_pool = bwd ? d.d_out_pool : nullptr;
+  a.pool_k = (a.out_pool || a.d_out_pool) ? d.pool_k : 0;
+  a.rows = d.rows; a.N = d.N; a.Ns = has_skip ? d.Ns : d.N; a.act = d.act; a.eps = d.eps;
+  set_dropout(a, d.drop_p);
   a.seed_lo = static_cast<unsigned>(d.seed); a.seed_hi = static_cast<unsigned>(d.seed >> 32);
   a.skip_mode = pick_skip(a.N, a.Ns, has_skip);
   a.reverse = d.reverse ? 1 : 0;
@@ -805,11 +769,20 @@ int spectre_norm_act_fwd(const spectre_norm_act_t* d, void* stream) {
   if (int rc = validate("spectre_norm_act_fwd", d, false)) return rc;
   Args a = to_args(*d, false);
   const bool bf = d->act_dtype == SPECTRE_DTYPE_BF16;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (bf && fast_enabled()) {
+    int rc = SPECTRE_OK;
+    if (fast_fwd_launch(a, st, &rc)) {
+      if (rc != SPECTRE_OK) return rc;
+      last_launch_count() = 1;
+      last_error().clear();
+      return SPECTRE_OK;
+    }
+  }
   const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, a.skip_mode != kSkipNone, bf ? 2 : 4, false, false, 2,
                                 a.skip_mode == kSkipGeneral);
   a.tpr = sh.tpr; a.rpc = sh.rpc; a.stages = sh.stages; a.stage_bytes = sh.stage_bytes;
   const int grid = grid_for(a.rows, sh), block = sh.tpr * sh.rpc;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   const KernelFn kern = table().fwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode];
   if (sh.smem > kMaxSmem || ensure_dynamic_smem(reinterpret_cast<const void*>(kern), kMaxSmem) != cudaSuccess)
     return fail(SPECTRE_E_SHAPE, "spectre_norm_act_fwd: N=%d Ns=%d needs %zu B of shared memory (limit %d)", a.N, a.Ns, sh.smem, kMaxSmem);
@@ -843,13 +816,27 @@ size_t spectre_norm_act_bwd_workspace_bytes(long long rows, int N) {
         const size_t b = static_cast<size_t>(grid_for(rows, sh)) * 3 * N * sizeof(float);
         if (b > best) best = b;
       }
-  return best;
+  const size_t fast = static_cast<size_t>(fast_bwd_grid_bound()) * 3 * N * sizeof(float);
+  return fast > best ? fast : best;
 }
 
 int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
   if (int rc = validate("spectre_norm_act_bwd", d, true)) return rc;
   Args a = to_args(*d, true);
   const bool bf = d->act_dtype == SPECTRE_DTYPE_BF16;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (bf && fast_enabled()) {
+    int rc = SPECTRE_OK, fgrid = 0;
+    if (fast_bwd_launch(a, d->workspace ? d->workspace_bytes : 0, st, &rc, &fgrid)) {
+      if (rc != SPECTRE_OK) return rc;
+      reduce_gamma_beta_kernel<<<(a.nacc * a.N + 7) / 8, 256, 0, st>>>(a.part, d->dgamma, d->dbeta, d->dcolsum, a.N, a.nacc, fgrid);
+      last_launch_count() = 2;
+      const cudaError_t err = cudaGetLastError();
+      if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "norm_act_bwd launch: %s", cudaGetErrorString(err));
+      last_error().clear();
+      return SPECTRE_OK;
+    }
+  }
   const Shape sh = launch_shape(a.N, a.Ns, a.in1 != nullptr, false, bf ? 2 : 4, true, a.dout2 != nullptr, a.nacc,
                                 a.skip_mode == kSkipGeneral);
   a.tpr = sh.tpr; a.rpc = sh.rpc; a.stages = sh.stages; a.stage_bytes = sh.stage_bytes;
@@ -857,7 +844,6 @@ int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
   if (!d->workspace || d->workspace_bytes < static_cast<size_t>(grid) * a.nacc * a.N * sizeof(float))
     return fail(SPECTRE_E_WORKSPACE, "spectre_norm_act_bwd: workspace %zu B < required %zu B", d->workspace_bytes,
                 static_cast<size_t>(grid) * a.nacc * a.N * sizeof(float));
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   const KernelFn kern = table().bwd[bf ? 1 : 0][sh.vpt - 1][a.act ? 1 : 0][a.skip_mode];
   if (sh.smem > kMaxSmem || ensure_dynamic_smem(reinterpret_cast<const void*>(kern), kMaxSmem) != cudaSuccess)
     return fail(SPECTRE_E_SHAPE, "spectre_norm_act_bwd: N=%d Ns=%d needs %zu B of shared memory (limit %d)", a.N, a.Ns, sh.smem, kMaxSmem);

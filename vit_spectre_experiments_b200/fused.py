@@ -37,8 +37,10 @@ def _ptr(t):
 
 
 # ------------------------------------------------------------------ raw (non-autograd) kernel calls
-def na_fwd(in0, gamma, beta, in1=None, skip=None, eps=1e-5, act=0, drop_p=0.0, seed=0, reverse=False):
-    """One forward tail.  Returns ``(out, mean, rstd)``; operands must already share in0's dtype."""
+def na_fwd(in0, gamma, beta, in1=None, skip=None, eps=1e-5, act=0, drop_p=0.0, seed=0, reverse=False, pool_k=0):
+    """One forward tail.  Returns ``(out, mean, rstd)``; operands must already share in0's dtype.
+    ``pool_k`` in (2, 4, 8): also returns ``out_pool [rows, N / pool_k]`` (mean of every ``pool_k`` consecutive columns
+    of ``out``) as a fourth value."""
     lib = _lib.load()
     if not in0.is_cuda:
         raise RuntimeError("norm_act: CUDA (sm_100a) only; there is no CPU fallback")
@@ -55,18 +57,28 @@ def na_fwd(in0, gamma, beta, in1=None, skip=None, eps=1e-5, act=0, drop_p=0.0, s
     d.rows, d.N, d.Ns = rows, N, (skip.shape[-1] if skip is not None else N)
     d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
     d.reverse = int(bool(reverse))
+    out_pool = None
+    if pool_k:
+        out_pool = torch.empty(rows, N // pool_k, dtype=in0.dtype, device=in0.device)
+        d.out_pool, d.pool_k = _ptr(out_pool), int(pool_k)
+    nbytes = (in0.numel() * (2 + (in1 is not None)) + (skip.numel() if skip is not None else 0)
+              + (out_pool.numel() if pool_k else 0)) * in0.element_size()
     with torch.cuda.device(in0.device):
-        with _timed("norm_act_fwd", (rows, N, in0.element_size())):
+        tag = f"norm_act_fwd:N{N}:Ns{d.Ns if skip is not None else 0}:act{int(act)}:in1{int(in1 is not None)}"
+        with _timed(tag, (rows, N, in0.element_size(), nbytes)):
             rc = lib.spectre_norm_act_fwd(ctypes.byref(d), _stream_ptr(in0.device))
     _lib.check(rc, "spectre_norm_act_fwd")
     _lib.count_launches()
+    if pool_k:
+        return out, mean, rstd, out_pool
     return out, mean, rstd
 
 
 def na_bwd(dout, in0, gamma, beta, mean, rstd, in1=None, skip_shape=None, eps=1e-5, act=0, drop_p=0.0, seed=0,
-           dout2=None, colsum=False, reverse=False):
+           dout2=None, colsum=False, reverse=False, d_out_pool=None, pool_k=0):
     """One backward tail.  Returns ``(d_in0, d_skip | None, dgamma, dbeta, dcolsum | None)``; ``d_in0`` is also
-    the gradient of ``in1``; ``dcolsum`` = column sums of ``d_in0`` (fp32)."""
+    the gradient of ``in1``; ``dcolsum`` = column sums of ``d_in0`` (fp32).  ``d_out_pool [rows, N / pool_k]``: gradient
+    that arrived through the forward's pooled copy (added to ``dout`` inside the kernel)."""
     lib = _lib.load()
     N = in0.shape[-1]
     rows = in0.numel() // N
@@ -82,11 +94,16 @@ def na_bwd(dout, in0, gamma, beta, mean, rstd, in1=None, skip_shape=None, eps=1e
     d.rows, d.N, d.Ns = rows, N, (skip_shape[-1] if skip_shape is not None else N)
     d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
     d.reverse = int(bool(reverse))
+    if d_out_pool is not None:
+        d.d_out_pool, d.pool_k = _ptr(d_out_pool), int(pool_k)
+    nbytes = (in0.numel() * (3 + (in1 is not None) + (dout2 is not None)) + (d_skip.numel() if d_skip is not None else 0)
+              + (d_out_pool.numel() if d_out_pool is not None else 0)) * in0.element_size()
     with torch.cuda.device(dev):
         nws = lib.spectre_norm_act_bwd_workspace_bytes(rows, N)
         ws = torch.empty(max(nws, 16), dtype=torch.uint8, device=dev)
         d.workspace, d.workspace_bytes = ws.data_ptr(), nws
-        with _timed("norm_act_bwd", (rows, N, in0.element_size())):
+        tag = f"norm_act_bwd:N{N}:Ns{d.Ns if d_skip is not None else 0}:act{int(act)}:in1{int(in1 is not None)}"
+        with _timed(tag, (rows, N, in0.element_size(), nbytes)):
             rc = lib.spectre_norm_act_bwd(ctypes.byref(d), _stream_ptr(dev))
     _lib.check(rc, "spectre_norm_act_bwd")
     _lib.count_launches()
@@ -157,9 +174,19 @@ class _EncoderLayer(torch.autograd.Function):
         x2d, m2d = x.view(rows, E), m.view(rows, E)
         x1, mean1, rstd1 = na_fwd(m2d, n1w, n1b, skip=x2d, eps=eps[0])
         h1 = torch.addmm(b1c, x1, w1c.t())
-        a1, mean2, rstd2 = na_fwd(h1, l1w, l1b, skip=x1, eps=eps[1], act=1, drop_p=p1, seed=seed1)
+        # hidden = k * E with k in (2, 4, 8): linear3's skip AdaptiveAvgPool1d(E)(a1) is the mean of every k consecutive
+        # columns -- the kernel that writes a1 emits it (out_pool), so the second tail reads E columns per row, not k * E
+        hid = w1.shape[0]
+        pk = hid // E if (hid % E == 0 and hid // E in (2, 4, 8) and hid % (8 * (hid // E)) == 0) else 0
+        ctx.pool_k = pk
+        if pk:
+            a1, mean2, rstd2, a1p = na_fwd(h1, l1w, l1b, skip=x1, eps=eps[1], act=1, drop_p=p1, seed=seed1, pool_k=pk)
+        else:
+            a1, mean2, rstd2 = na_fwd(h1, l1w, l1b, skip=x1, eps=eps[1], act=1, drop_p=p1, seed=seed1)
+            a1p = a1
         h2 = torch.addmm(b3c, a1, w3c.t())
-        ff, mean3, rstd3 = na_fwd(h2, l3w, l3b, skip=a1, eps=eps[2], act=1, drop_p=p2, seed=seed2)
+        ff, mean3, rstd3 = na_fwd(h2, l3w, l3b, skip=a1p, eps=eps[2], act=1, drop_p=p2, seed=seed2)
+        del a1p
         x2, mean4, rstd4 = na_fwd(x1, n2w, n2b, in1=ff, eps=eps[3])
         ctx.save_for_backward(x, mp, m, x1, h1, a1, h2, ff, w1c, w3c, n1w, n1b, l1w, l1b, l3w, l3b, n2w, n2b,
                               mean1, rstd1, mean2, rstd2, mean3, rstd3, mean4, rstd4)
@@ -183,13 +210,22 @@ class _EncoderLayer(torch.autograd.Function):
         # x2 = LN2(x1 + ff): one gradient for both addends; the two parts of the upstream gradient are summed in the kernel
         d_z, _, dn2w, dn2b, _ = na_bwd(d_x2, x1, n2w, n2b, mean4, rstd4, in1=ff, eps=eps[3], dout2=d_x2b)
         # ff = GELU(LN(h2)) + pool_down(a1)
-        d_h2, d_a1, dl3w, dl3b, db3 = na_bwd(d_z, h2, l3w, l3b, mean3, rstd3, skip_shape=(rows, hid), eps=eps[2], act=1,
-                                             drop_p=p2, seed=seed2, colsum=True)
-        dw3 = torch.mm(d_h2.t(), a1)
-        d_a1.addmm_(d_h2, w3c)                                     # skip path + GEMM path in the GEMM epilogue (in place)
+        pk = ctx.pool_k
+        if pk:
+            # the skip gradient stays [rows, E] (gradient of the pooled copy); the first tail's backward spreads it
+            d_h2, d_a1p, dl3w, dl3b, db3 = na_bwd(d_z, h2, l3w, l3b, mean3, rstd3, skip_shape=(rows, E), eps=eps[2], act=1,
+                                                  drop_p=p2, seed=seed2, colsum=True)
+            dw3 = torch.mm(d_h2.t(), a1)
+            d_a1 = torch.mm(d_h2, w3c)
+        else:
+            d_h2, d_a1, dl3w, dl3b, db3 = na_bwd(d_z, h2, l3w, l3b, mean3, rstd3, skip_shape=(rows, hid), eps=eps[2],
+                                                 act=1, drop_p=p2, seed=seed2, colsum=True)
+            dw3 = torch.mm(d_h2.t(), a1)
+            d_a1.addmm_(d_h2, w3c)                                 # skip path + GEMM path in the GEMM epilogue (in place)
+            d_a1p = None
         # a1 = drop(GELU(LN(h1)) + pool_up(x1))
         d_h1, d_x1, dl1w, dl1b, db1 = na_bwd(d_a1, h1, l1w, l1b, mean2, rstd2, skip_shape=(rows, E), eps=eps[1], act=1,
-                                             drop_p=p1, seed=seed1, colsum=True)
+                                             drop_p=p1, seed=seed1, colsum=True, d_out_pool=d_a1p, pool_k=pk)
         dw1 = torch.mm(d_h1.t(), x1)
         d_x1.addmm_(d_h1, w1c)
         # x1 = LN1(m) + x: upstream = d_x1 (skip + GEMM paths) + d_z (LN2 path), summed inside the kernel;
