@@ -6,8 +6,9 @@
 
 One JSON line on rank 0.  "step" = one optimisation step (forward, loss, backward with the fused
 filter-gradient reduction, DDP all-reduce, fused AdamW) of the configured Spectre-ViT on one batch per
-GPU.  Default workload: BASELINE.json configs[3] (ViT-S/16 FFT-mix, 224^2 -> 14x14 grid, bf16, batch 256
-per GPU) -- the configuration the north-star's scaling target is quoted on.
+GPU.  Default workload: BASELINE.json configs[3] (ViT-S/16 FFT-mix, 224^2 -> 14x14 grid, bf16, batch 2048 per GPU =
+configs/vit_s16_fft.py:bench_batch_size; --batch 256 gives SURVEY.md's batch) -- the configuration the north-star's
+scaling target is quoted on.
 
   value     images/s, inputs resident in HBM, CUDA events, max over ranks
   e2e       same through the public API with HOST buffers: every step copies the batch from pinned host
@@ -40,7 +41,7 @@ WORKLOADS = {
     "c2": "Spectre-ViT tiny FFT-mix, MNIST-shaped 28x28, patch 4 (7x7 grid), fp32",
     "c3": "Spectre-ViT DWT-mix (Haar) CIFAR-100-shaped, bf16",
     "c4": "ViT-S/16 FFT-mix 224^2 (14x14 grid) synthetic ImageNet-shaped, bf16",
-    "c5": "ViT-B/16 spectral student distilled from random-init ViT-B/16 teacher, 224^2, bf16",
+    "c5": "ViT-B/16 spectral student distilled from random-init DINOv3 ViT-B/16 teacher, 224^2, bf16",
 }
 
 
@@ -103,14 +104,59 @@ def oracle_factory(kind):
     return lambda d_model, seq, nhead, out: cls(d_model, seq, nhead, out)
 
 
+REF_DIR = os.path.join(ROOT, "baseline", "_ref")   # the unmodified reference, installed by baseline/install_ref.sh
+
+
+def reference_available() -> bool:
+    return os.path.isdir(os.path.join(REF_DIR, "spectre_vit")) and os.path.isdir(os.path.join(REF_DIR, "dinov3"))
+
+
+def reference_teacher(cfg):
+    """Config 5's teacher as the reference builds it (spectre_vit/repl/train.py:60-83, distillation.py:5-22):
+    ``DinoClassifier(dinov3_vitb16(pretrained=False), num_classes, embed_dim=768)``, random init, frozen."""
+    if REF_DIR not in sys.path:
+        sys.path.insert(0, REF_DIR)
+    from dinov3.hub.backbones import dinov3_vitb16
+    from spectre_vit.distillation import DinoClassifier
+
+    return DinoClassifier(backbone=dinov3_vitb16(pretrained=False), num_classes=cfg.num_classes,
+                          embed_dim=cfg.teacher_embed_dim)
+
+
+def reference_model(cfg):
+    """The reference's OWN ``SpectreViT`` (spectre_vit/models/spectre/spectre.py:159-202) with the oracle's torch.fft /
+    Haar composition placed in every layer's ``mix_layer`` slot (the reference has no module of its own there)."""
+    if REF_DIR not in sys.path:
+        sys.path.insert(0, REF_DIR)
+    from spectre_vit.models.spectre.spectre import SpectreViT as RefViT
+
+    m = RefViT(img_size=cfg.img_size, patch_size=cfg.patch_size, in_channels=cfg.in_channels, num_classes=cfg.num_classes,
+               embed_dim=cfg.embed_dim, num_encoders=cfg.num_encoders, num_heads=cfg.num_heads, hidden_dim=cfg.hidden_dim,
+               dropout=cfg.dropout, activation=cfg.activation)
+    make = oracle_factory(cfg.mixer)
+    T = (cfg.img_size // cfg.patch_size) ** 2 + 1
+    for layer in m.encoder_blocks.layers:
+        layer.mix_layer = make(cfg.embed_dim, T, cfg.num_heads, cfg.embed_dim)
+    return m
+
+
 def cpu_reference_leg(cfg, steps, warmup, batch, label):
-    """The reference's PyTorch path on the host cores (oracle port): fwd + bwd + AdamW, fp32."""
+    """The reference's PyTorch path on the host cores: fwd + bwd + AdamW, fp32.  With baseline/_ref present the model
+    (and config 5's teacher) are the reference's own classes (kind "reference"); otherwise the repo's mirror of them
+    (kind "port", pinned to the reference by tests/golden)."""
     from vit_spectre_experiments_b200.train import Trainer
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     cfg_cpu = type(cfg)(**{**vars(cfg), "precision": "fp32"})
-    tr = Trainer(cfg_cpu, "cpu", mixer=oracle_factory(cfg.mixer), ddp=False)
+    kind = "port"
+    model = teacher = None
+    if reference_available():
+        torch.manual_seed(cfg.random_seed)
+        model, kind = reference_model(cfg_cpu), "reference"
+        if getattr(cfg, "distill", False):
+            teacher = reference_teacher(cfg_cpu)
+    tr = Trainer(cfg_cpu, "cpu", mixer=oracle_factory(cfg.mixer), ddp=False, model=model, teacher=teacher)
     img, lab = tr.synthetic_batch(batch)
     for _ in range(warmup):
         tr.step(img, lab)
@@ -118,9 +164,11 @@ def cpu_reference_leg(cfg, steps, warmup, batch, label):
     for _ in range(steps):
         tr.step(img, lab)
     dt = time.perf_counter() - t0
-    return {"value": round(batch * steps / dt, 2), "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"{label}: {steps} steps x {batch} images fwd+bwd+AdamW on CPU fp32 (torch.fft has no bf16), "
-                      f"{warmup} warm-up, {dt:.1f} s"}, dt / steps * 1e3
+    what = ("reference SpectreViT class + oracle mixer in its slot" if kind == "reference"
+            else "mirror of the reference classes + oracle mixer")
+    return {"value": round(batch * steps / dt, 2), "unit": "images/s", "cores": torch.get_num_threads(), "kind": kind,
+            "sample": f"{label}: {what}; {steps} steps x {batch} images fwd+bwd+AdamW on CPU fp32 (torch.fft has no "
+                      f"bf16), {warmup} warm-up, {dt:.1f} s"}, dt / steps * 1e3
 
 
 def main():
@@ -179,7 +227,14 @@ def main():
     from vit_spectre_experiments_b200.functional import TIMER
 
     _lib.load()
-    tr = Trainer(cfg, dev)
+    teacher = None
+    if getattr(cfg, "distill", False):
+        if reference_available():
+            teacher = reference_teacher(cfg)
+            config["teacher"] = "reference DinoClassifier(dinov3_vitb16(pretrained=False)) from baseline/_ref, frozen"
+        else:
+            config["teacher"] = "stock ViT-B/16 of the same sizes (baseline/_ref absent: run baseline/install_ref.sh)"
+    tr = Trainer(cfg, dev, teacher=teacher)
     img, lab = tr.synthetic_batch(batch, rank)
     warm = max(3, args.warmup)
     K = args.steps
@@ -276,7 +331,31 @@ def main():
                     "frac": round(k["GBps"] / peaks["hbm_gbs"], 4), "peak_source": f"{peak_src} (MEASURED_PEAKS.json)",
                     "algo_bytes_per_launch": k["algo_bytes"], "mean_launch_ms": k["mean_ms"],
                     "mean_call_ms": k["mean_call_ms"], "frac_whole_call": round(k["GBps_call"] / peaks["hbm_gbs"], 4),
-                    "traffic": traffic.get(f"{args.config}:{key}")}
+                    "traffic": traffic.get(f"{args.config}:{key}"),
+                    "traffic_source": "profiles/ncu_traffic.json (one ncu --set full capture of this kernel at this shape; "
+                                      "not re-measured in this run)"}
+        # ---- model-level roofline: t_roof/step = memory-bound bytes / HBM peak + GEMM flops /
+        # sustained tensor peak.  GEMM flops: the two Linears of every encoder layer + patch projection + head, x3 for
+        # forward + both backward GEMMs.  Memory-bound bytes: the algorithmic bytes of every own kernel launched in a
+        # step (mixers + row-wise tails, counted from the calls above) + the image read + AdamW's 28 B per parameter.
+        nparam = sum(p.numel() for p in tr.model.parameters())
+        hid, P, Cin = cfg.hidden_dim, cfg.patch_size, cfg.in_channels
+        gemm_flops_img = 3 * 2 * (L * 2 * T * E * hid + (T - 1) * Cin * P * P * E + E * cfg.num_classes)
+        own_bytes_step = sum(k["algo_bytes"] * k["launches"] for k in kernels.values()) / K
+        mem_bytes_step = own_bytes_step + batch * Cin * cfg.img_size ** 2 * 4 + nparam * 28
+        tf_peak = peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1395.1))
+        if cfg.precision != "bf16":
+            tf_peak = tf_peak / 2      # fp32 configs run their GEMMs as TF32: half the bf16 tensor rate (nominal)
+        t_gemm = gemm_flops_img * batch / (tf_peak * 1e12)
+        t_mem = mem_bytes_step / (peaks["hbm_gbs"] * 1e9)
+        step_s = ms_total / K / 1e3
+        model_roof = {
+            "gemm_gflop_per_image": round(gemm_flops_img / 1e9, 3), "memory_bound_MB_per_image": round(mem_bytes_step / batch / 1e6, 3),
+            "tensor_peak_tflops": round(tf_peak, 1), "hbm_peak_gbs": peaks["hbm_gbs"],
+            "gemm_only_roof_img_s": round(batch / t_gemm, 1), "serial_roof_img_s": round(batch / (t_gemm + t_mem), 1),
+            "frac_of_gemm_roof": round(t_gemm / step_s, 4), "frac_of_serial_roof": round((t_gemm + t_mem) / step_s, 4),
+            "note": "per GPU; serial roof = GEMMs at the sustained tensor peak + every memory-bound op at the HBM copy peak, no overlap",
+        }
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cpu, _ = cpu_reference_leg(cfg, 3, 1, cpu_batch, args.config)
@@ -288,7 +367,8 @@ def main():
             "e2e": {"value": round(batch * world * K / (ms_e2e / 1e3), 1), "unit": "images/s",
                     "h2d_bytes_per_step": (himg.numel() * himg.element_size() + hlab.numel() * hlab.element_size()) * world,
                     "d2h_bytes_per_step": 4 * world, "ms_per_step": round(ms_e2e / K, 3)},
-            "gpu_launches": launches, "roofline": roof, "kernels": kernels, "cpu_baseline": cpu, "clocks": clocks,
+            "gpu_launches": launches, "roofline": roof, "model_roofline": model_roof, "kernels": kernels,
+            "cpu_baseline": cpu, "clocks": clocks,
             "final_loss": round(final_loss, 4),
         }
         print(json.dumps(out), flush=True)

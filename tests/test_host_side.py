@@ -137,6 +137,8 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src, f
+                # nor the installed reference (baseline/_ref): only bench.py builds the reference model / teacher from it
+                assert "baseline" not in src and "spectre_vit." not in src.replace("spectre_vit/", ""), f
 
 
 @pytest.mark.parametrize("T,E", [(65, 64), (50, 48), (197, 24)])

@@ -171,12 +171,13 @@ __device__ __forceinline__ unsigned drop_mask8(const Args& a, unsigned rseed, un
   if (x >= a.drop_q32) return 0u;
   return drop_mask8_slow(a, x);
 }
-// seed of a row: folds the high bits of the 64-bit seed and the row index so the column index can stay 32-bit
+// seed of a row (one 32-bit mix of the row index under the 64-bit call seed; drop_mask8 mixes the vector index in)
 __device__ __forceinline__ unsigned row_seed(const Args& a, long long row) {
-  unsigned long long z = (static_cast<unsigned long long>(a.seed_hi) << 32 | a.seed_lo) + static_cast<unsigned long long>(row) * 0x9E3779B97F4A7C15ull;
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z ^= z >> 27;
-  return static_cast<unsigned>(z >> 16);
+  unsigned x = static_cast<unsigned>(row) * 0x9E3779B1u + a.seed_lo;
+  x ^= x >> 16;
+  x *= 0x7feb352du;
+  x ^= x >> 15;
+  return x + (a.seed_hi ^ static_cast<unsigned>(row >> 32)) * 0x846ca68bu;
 }
 
 // ------------------------------------------------------------------ fast path (normact_fast.cu)

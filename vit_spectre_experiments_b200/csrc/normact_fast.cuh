@@ -81,8 +81,9 @@ __device__ __forceinline__ u64 ldg2(const float* p) {   // two consecutive float
 }
 
 // Sum of (a, b) over the TPR threads of a row; every thread of the row gets the totals.
-// TPR <= 32: rows are aligned lane groups, shuffles only.  TPR > 32: warp totals meet in shared memory behind one
-// CTA-wide barrier (every row group of the CTA runs the same trip count); `slot` alternates between calls.
+// TPR <= 32: rows are aligned lane groups, shuffles only.  TPR > 32: warp totals meet in shared memory behind a named
+// barrier of the row's own warps (ids 1 .. RPC); `slot` alternates between calls, the CTA-wide barrier that ends every
+// iteration orders the reuse.
 template <int TPR, int RW>
 __device__ __forceinline__ void row_sum2(float& a, float& b, float (*red)[2][RW], int slot, int rg) {
   constexpr int kTop = TPR >= 32 ? 16 : TPR / 2;
@@ -98,7 +99,7 @@ __device__ __forceinline__ void row_sum2(float& a, float& b, float (*red)[2][RW]
       red[slot][0][w] = a;
       red[slot][1][w] = b;
     }
-    __syncthreads();
+    ptx::named_bar_sync(1 + rg, TPR);   // only the warps of this row meet here; rows of the CTA run on independently
     float sa = red[slot][0][rg * WPR], sb = red[slot][1][rg * WPR];
 #pragma unroll
     for (int k = 1; k < WPR; ++k) {

@@ -32,10 +32,8 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
   const bool drop = a.drop_p > 0.f;
   const long long groups = (a.rows + RPC - 1) / RPC;
   const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
-  auto group_of = [&](int it) {
-    const long long g = blockIdx.x + static_cast<long long>(it) * gridDim.x;
-    return a.reverse ? groups - 1 - g : g;
-  };
+  const long long gstep = static_cast<long long>(gridDim.x) * RPC * (a.reverse ? -1 : 1);
+  const long long first0 = (a.reverse ? groups - 1 - blockIdx.x : static_cast<long long>(blockIdx.x)) * RPC;
   // ring stage: dout | in0 | (in1) | (dout2) | (d_out_pool: N / 4 columns)
   constexpr int kOp = RPC * N * 2;
   const int off_in1 = 2 * kOp;
@@ -43,7 +41,7 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
   const int off_dp = off_d2 + (has_d2 ? kOp : 0);
 
   auto issue = [&](int it, int stg) {
-    const long long row0 = group_of(it) * RPC;
+    const long long row0 = first0 + it * gstep;
     const long long left = a.rows - row0;
     const uint32_t nr = static_cast<uint32_t>(left < RPC ? left : RPC);
     uint8_t* st = ring + stg * a.stage_bytes;
@@ -80,23 +78,20 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
   const u64 cphi = splat(kInvSqrt2Pi), cexp = splat(-kHalfLog2e), ks2 = splat(a.keep_scale), quarter2 = splat(0.25f);
   constexpr float inv_n = 1.0f / N;
   float mean_n = 0.f, rstd_n = 0.f;
-  {
-    const long long row = group_of(0) * RPC + rg;
-    if (n_it > 0 && row < a.rows) { mean_n = a.mean[row]; rstd_n = a.rstd[row]; }
-  }
+  long long row = first0 + rg;
+  if (n_it > 0 && row < a.rows) { mean_n = a.mean[row]; rstd_n = a.rstd[row]; }
   int stg = 0;
   uint32_t phase = 0;
-  for (int it = 0; it < n_it; ++it) {
+  const uint8_t* st = ring;
+  for (int it = 0; it < n_it; ++it, row += gstep) {
     if (threadIdx.x == 0 && it + S - 1 < n_it) issue(it + S - 1, stg == 0 ? S - 1 : stg - 1);
-    const long long row = group_of(it) * RPC + rg;
     const bool live = row < a.rows;
     const float mean = mean_n, rstd = rstd_n;
     {
-      const long long rown = group_of(it + 1) * RPC + rg;
+      const long long rown = row + gstep;
       if (it + 1 < n_it && rown < a.rows) { mean_n = a.mean[rown]; rstd_n = a.rstd[rown]; }
     }
     ptx::mbar_wait(&full[stg], phase);
-    const uint8_t* st = ring + stg * a.stage_bytes;
     const u64 rs2 = splat(rstd), sh2 = splat(-mean * rstd);
     const unsigned rseed = drop ? row_seed(a, row) : 0u;
     __nv_bfloat16* dsrow = static_cast<__nv_bfloat16*>(a.d_skip) + row * NS;
@@ -196,7 +191,8 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
       }
     }
     __syncthreads();   // stage consumed
-    if (++stg == S) { stg = 0; phase ^= 1u; }
+    st += a.stage_bytes;
+    if (++stg == S) { stg = 0; phase ^= 1u; st = ring; }
   }
   // ---- fold the row groups of the CTA in a fixed order (through the now idle ring, one accumulator kind at a time)
   float* fold = reinterpret_cast<float*>(ring);

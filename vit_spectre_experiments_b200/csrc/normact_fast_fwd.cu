@@ -30,15 +30,14 @@ __global__ void __launch_bounds__(256, 2) fast_fwd_kernel(const Args a) {
   const bool drop = a.drop_p > 0.f;
   const long long groups = (a.rows + RPC - 1) / RPC;
   const int n_it = static_cast<int>((groups - blockIdx.x + gridDim.x - 1) / gridDim.x);
-  auto group_of = [&](int it) {
-    const long long g = blockIdx.x + static_cast<long long>(it) * gridDim.x;
-    return a.reverse ? groups - 1 - g : g;
-  };
+  // first row of the group of iteration `it`: first0 + it * gstep (ascending, or descending from the last group)
+  const long long gstep = static_cast<long long>(gridDim.x) * RPC * (a.reverse ? -1 : 1);
+  const long long first0 = (a.reverse ? groups - 1 - blockIdx.x : static_cast<long long>(blockIdx.x)) * RPC;
   const int off_in1 = RPC * N * 2;
   const int off_skip = off_in1 * (has_in1 ? 2 : 1);
 
   auto issue = [&](int it, int stg) {   // one thread: the group's rows are contiguous in every operand
-    const long long row0 = group_of(it) * RPC;
+    const long long row0 = first0 + it * gstep;
     const long long left = a.rows - row0;
     const uint32_t nr = static_cast<uint32_t>(left < RPC ? left : RPC);
     uint8_t* st = ring + stg * a.stage_bytes;
@@ -58,15 +57,25 @@ __global__ void __launch_bounds__(256, 2) fast_fwd_kernel(const Args a) {
 
   const u64 c0 = splat(kGeluC0), c1 = splat(kGeluC1), c2 = splat(kGeluC2), half2 = splat(0.5f);
   const u64 ks2 = splat(a.keep_scale);
+  // gamma / beta of this thread's columns stay in registers for the whole kernel (loading them per row group kept the
+  // LSU data pipe 72-86 % busy and bounded the kernel: profiles/r02_ncu_normact_fast_v1.txt)
+  u64 gam[VPT][4], bet[VPT][4];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      gam[i][k] = ldg2(a.gamma + (t + i * TPR) * 8 + 2 * k);
+      bet[i][k] = ldg2(a.beta + (t + i * TPR) * 8 + 2 * k);
+    }
   constexpr float inv_n = 1.0f / N;
   int stg = 0;
   uint32_t phase = 0;
-  for (int it = 0; it < n_it; ++it) {
+  long long row = first0 + rg;
+  const uint8_t* st = ring;
+  for (int it = 0; it < n_it; ++it, row += gstep) {
     if (threadIdx.x == 0 && it + S - 1 < n_it) issue(it + S - 1, stg == 0 ? S - 1 : stg - 1);   // the stage freed by it-1
     ptx::mbar_wait(&full[stg], phase);
-    const long long row = group_of(it) * RPC + rg;
     const bool live = row < a.rows;
-    const uint8_t* st = ring + stg * a.stage_bytes;
     const uint4* r0 = reinterpret_cast<const uint4*>(st) + rg * NV;
     const uint4* r1 = reinterpret_cast<const uint4*>(st + off_in1) + rg * NV;
     // ---- statistics in one pass about a pivot from the row itself (its first element): no cancellation in
@@ -117,7 +126,7 @@ __global__ void __launch_bounds__(256, 2) fast_fwd_kernel(const Args a) {
       u64 r[4];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const u64 u = fma2(fma2(d[i][k], rs2, sh2), ldg2(a.gamma + j0 + 2 * k), ldg2(a.beta + j0 + 2 * k));
+        const u64 u = fma2(fma2(d[i][k], rs2, sh2), gam[i][k], bet[i][k]);
         if constexpr (ACT) {
           const u64 u2 = mul2(u, u);
           const u64 th = tanh2(mul2(u, fma2(fma2(c2, u2, c1), u2, c0)));
@@ -157,7 +166,8 @@ __global__ void __launch_bounds__(256, 2) fast_fwd_kernel(const Args a) {
       }
     }
     __syncthreads();   // every thread is done with this stage: the producer may refill it
-    if (++stg == S) { stg = 0; phase ^= 1u; }
+    st += a.stage_bytes;
+    if (++stg == S) { stg = 0; phase ^= 1u; st = ring; }
   }
 }
 

@@ -87,15 +87,20 @@ class Trainer:
     (DDP all-reduce overlapped) -> fused AdamW.  ``step`` returns the loss tensor without syncing."""
 
     def __init__(self, cfg: SimpleNamespace, device, *, mixer: str | None = None, model: nn.Module | None = None,
-                 ddp: bool | None = None, seed: int | None = None):
+                 ddp: bool | None = None, seed: int | None = None, teacher: nn.Module | None = None):
         self.cfg, self.device = cfg, torch.device(device)
         torch.manual_seed(cfg.random_seed if seed is None else seed)
         self.model = (model if model is not None else build_model(cfg, mixer)).to(self.device)
         self.bf16 = getattr(cfg, "precision", "fp32") == "bf16" and self.device.type == "cuda"
         self.teacher = None
         if getattr(cfg, "distill", False):
-            self.teacher = TeacherViT(cfg.img_size, cfg.patch_size, cfg.in_channels, cfg.teacher_embed_dim,
-                                      cfg.teacher_depth, cfg.teacher_heads, cfg.num_classes).to(self.device).eval()
+            # `teacher`: any frozen module with forward(img) -> logits (or (logits, features) with return_features=True),
+            # e.g. the reference's DinoClassifier(dinov3_vitb16(pretrained=False)) (spectre_vit/distillation.py:5-22,
+            # repl/train.py:60-83) built by the caller; default: a stock ViT of the same sizes
+            if teacher is None:
+                teacher = TeacherViT(cfg.img_size, cfg.patch_size, cfg.in_channels, cfg.teacher_embed_dim,
+                                     cfg.teacher_depth, cfg.teacher_heads, cfg.num_classes)
+            self.teacher = teacher.to(self.device).eval()
             for p in self.teacher.parameters():
                 p.requires_grad_(False)
         world = dist.get_world_size() if dist.is_initialized() else 1
