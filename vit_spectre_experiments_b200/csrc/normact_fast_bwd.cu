@@ -223,18 +223,21 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
 typedef void (*FastFn)(const Args);
 // (activation, accumulators) pairs that occur: LayerNorm alone -> (0, 2); GELU tail of a Linear -> (1, 3) with the
 // bias gradient as column sums, (1, 2) without.  Anything else falls back to the generic kernels.
-template <int VPT, int TPR, int RPC, int MODE>
-static FastFn pick_bwd_mode(int act, int nacc) {
-  if (!act && nacc == 2) return fast_bwd_kernel<VPT, TPR, RPC, MODE, 0, 2>;
-  if (act && nacc == 3) return fast_bwd_kernel<VPT, TPR, RPC, MODE, 1, 3>;
-  if (act && nacc == 2) return fast_bwd_kernel<VPT, TPR, RPC, MODE, 1, 2>;
+template <int VPT, int TPR, int RPC, int MODE, int ACT>
+static FastFn pick_bwd_mode(int nacc) {
+  if constexpr (ACT) {
+    if (nacc == 3) return fast_bwd_kernel<VPT, TPR, RPC, MODE, 1, 3>;
+    if (nacc == 2) return fast_bwd_kernel<VPT, TPR, RPC, MODE, 1, 2>;
+  } else {
+    if (nacc == 2) return fast_bwd_kernel<VPT, TPR, RPC, MODE, 0, 2>;
+  }
   return nullptr;
 }
-template <int VPT, int TPR, int RPC>
-static FastFn pick_bwd(int mode, int act, int nacc) {
-  if (mode == kSkipNone) return pick_bwd_mode<VPT, TPR, RPC, kSkipNone>(act, nacc);
-  if (mode == kSkipIdentity) return pick_bwd_mode<VPT, TPR, RPC, kSkipIdentity>(act, nacc);
-  if (mode == kSkipUp4) return pick_bwd_mode<VPT, TPR, RPC, kSkipUp4>(act, nacc);
+template <int VPT, int TPR, int RPC, int ACT>
+static FastFn pick_bwd(int mode, int nacc) {
+  if (mode == kSkipNone) return pick_bwd_mode<VPT, TPR, RPC, kSkipNone, ACT>(nacc);
+  if (mode == kSkipIdentity) return pick_bwd_mode<VPT, TPR, RPC, kSkipIdentity, ACT>(nacc);
+  if (mode == kSkipUp4) return pick_bwd_mode<VPT, TPR, RPC, kSkipUp4, ACT>(nacc);
   return nullptr;
 }
 
@@ -247,13 +250,20 @@ bool fast_bwd_launch(const Args& a0, size_t workspace_bytes, cudaStream_t st, in
   if (a0.d_out_pool && a0.pool_k != 4) return false;
   FastFn fn = nullptr;
   int threads = 0;
-#define SB200_SHAPE(V, T, R)                                   \
-  if (fs.vpt == V && fs.tpr == T) {                            \
-    fn = pick_bwd<V, T, R>(a0.skip_mode, a0.act ? 1 : 0, a0.nacc); \
-    threads = T * R;                                           \
+  // rows per CTA: the GELU kernels are issue-bound at 8-12 warps per SM (profiles/r02_ncu_normact_fast_v1.txt), so
+  // they take the largest CTA their register count allows; the LayerNorm-only kernels run at the HBM roof as they are
+#define SB200_SHAPE(V, T, R0, R1)                                              \
+  if (fs.vpt == V && fs.tpr == T) {                                            \
+    if (a0.act) {                                                              \
+      fn = pick_bwd<V, T, R1, 1>(a0.skip_mode, a0.nacc);                          \
+      threads = T * R1;                                                        \
+    } else {                                                                   \
+      fn = pick_bwd<V, T, R0, 0>(a0.skip_mode, a0.nacc);                          \
+      threads = T * R0;                                                        \
+    }                                                                          \
   }
-  SB200_SHAPE(3, 16, 16) SB200_SHAPE(3, 32, 8) SB200_SHAPE(2, 96, 4) SB200_SHAPE(2, 192, 2)
-  SB200_SHAPE(2, 16, 16) SB200_SHAPE(2, 32, 8) SB200_SHAPE(2, 64, 4) SB200_SHAPE(2, 128, 2)
+  SB200_SHAPE(3, 16, 16, 24) SB200_SHAPE(3, 32, 8, 12) SB200_SHAPE(2, 96, 4, 5) SB200_SHAPE(2, 192, 2, 2)
+  SB200_SHAPE(2, 16, 16, 24) SB200_SHAPE(2, 32, 8, 12) SB200_SHAPE(2, 64, 4, 6) SB200_SHAPE(2, 128, 2, 3)
 #undef SB200_SHAPE
   if (!fn) return false;
   Args a = a0;

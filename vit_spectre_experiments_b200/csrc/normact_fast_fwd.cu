@@ -16,14 +16,17 @@
 namespace sb200 {
 namespace na {
 
+// threads per CTA: 320 (two CTAs = 20 warps per SM within the register file) where the row split divides it, else 256
+constexpr int fwd_threads(int tpr) { return 320 % tpr == 0 ? 320 : 256; }
+
 template <int VPT, int TPR, int MODE, int ACT>
-__global__ void __launch_bounds__(256, 2) fast_fwd_kernel(const Args a) {
-  constexpr int N = 8 * VPT * TPR, RPC = 256 / TPR, NV = N / 8;
+__global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Args a) {
+  constexpr int N = 8 * VPT * TPR, RPC = fwd_threads(TPR) / TPR, NV = N / 8;
   constexpr int NS = MODE == kSkipIdentity ? N : MODE == kSkipUp4 ? N / 4 : 0;
   static_assert(MODE == kSkipNone || MODE == kSkipIdentity || MODE == kSkipUp4, "fast forward skip modes");
   extern __shared__ __align__(128) uint8_t ring[];
   __shared__ uint64_t full[kMaxStages];
-  __shared__ float red[2][2][8];
+  __shared__ float red[2][2][16];
   const int rg = threadIdx.x / TPR, t = threadIdx.x % TPR;
   const int S = a.stages;
   const bool has_in1 = a.in1 != nullptr;
@@ -196,7 +199,7 @@ bool fast_fwd_launch(const Args& a0, cudaStream_t st, int* rc) {
 #undef SB200_SHAPE
   if (!fn) return false;
   Args a = a0;
-  const int rpc = 256 / fs.tpr;
+  const int threads = fwd_threads(fs.tpr), rpc = threads / fs.tpr;
   const int ns = a.skip_mode == kSkipIdentity ? a.N : a.skip_mode == kSkipUp4 ? a.N / 4 : 0;
   const int row_bytes = a.N * 2 * (a.in1 ? 2 : 1) + ns * 2;
   a.tpr = fs.tpr; a.rpc = rpc;
@@ -214,7 +217,7 @@ bool fast_fwd_launch(const Args& a0, cudaStream_t st, int* rc) {
   const long long groups = (a.rows + rpc - 1) / rpc;
   const long long cap = static_cast<long long>(device_sm_count()) * 2;
   const int grid = static_cast<int>(groups < cap ? groups : cap);
-  fn<<<grid, 256, smem, st>>>(a);
+  fn<<<grid, threads, smem, st>>>(a);
   const cudaError_t err = cudaGetLastError();
   *rc = err == cudaSuccess ? SPECTRE_OK : fail(SPECTRE_E_CUDA, "norm_act_fwd (fast) launch: %s", cudaGetErrorString(err));
   return true;
