@@ -153,6 +153,26 @@ int spectre_permut_fwd(const void* x, const long long* perms, const float* signs
 int spectre_permut_bwd(const void* dout, const long long* inv_perms, const float* signs, void* dx,
                        int B, long long F, int heads, int act_dtype, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * SpectralPatchEmbed around its GEMM (spectre_vit/models/spectre/spectre.py:124-156).
+ * Re(rfft2(patch, norm="ortho")) (:136), the frequency gains (:139-141) and the projection (:144) are linear in the
+ * patch, so the host folds them into one matrix and the module becomes  tokens = patches @ M + b;
+ * out = dropout(cat(cls, tokens) + pos).  The GEMM is the caller's; these are the passes around it.
+ *
+ * spectre_patch_gather: the unfold of :127-131 + the (c, i, j) flattening of :144 + the cast to the stream dtype.
+ *   img float32 [B, C, Hi, Wi] -> out [B * (Hi/P) * (Wi/P), C * P * P] (act_dtype); P and Wi multiples of 4.
+ * spectre_embed_finish_fwd (:151-156): out[b, 0] = cls + pos[0]; out[b, 1 + i] = tok[b, i] + pos[1 + i]; dropout
+ *   (counter-based, as in spectre_norm_act_fwd).  tok [B, T-1, E] and out [B, T, E] in act_dtype, cls [E], pos [T, E] fp32.
+ * spectre_embed_finish_bwd: dtok[b, i] = mask * dout[b, 1 + i] / (1 - p);  dpos[t] = sum_b mask * dout[b, t] / (1 - p)
+ *   (fully overwritten; d cls = dpos[0], d bias of the projection = sum_{t >= 1} dpos[t]).  workspace >=
+ *   spectre_embed_finish_bwd_workspace_bytes(B, T, E): per-slab partials, summed in a fixed order. */
+int spectre_patch_gather(const float* img, void* out, int B, int C, int Hi, int Wi, int P, int act_dtype, void* stream);
+int spectre_embed_finish_fwd(const void* tok, const float* cls, const float* pos, void* out, int B, int T, int E,
+                             int act_dtype, float drop_p, unsigned long long seed, void* stream);
+int spectre_embed_finish_bwd(const void* dout, void* dtok, float* dpos, void* workspace, size_t workspace_bytes,
+                             int B, int T, int E, int act_dtype, float drop_p, unsigned long long seed, void* stream);
+size_t spectre_embed_finish_bwd_workspace_bytes(int B, int T, int E);
+
 /* Measurement hook (bench.py's per-kernel roofline): the next backward mixer call on this thread records `event`
  * (a cudaEvent_t) on its stream right after its main kernel, i.e. before the small partial-gradient reduction kernel.
  * spectre_debug_mark_pending() returns 1 and disarms the hook if no call consumed it (single-slab launches have no

@@ -354,3 +354,59 @@ def test_permut_mix_gather(cuda_device, B, T, E, heads, dtype):
     with pytest.raises(RuntimeError):
         inverse_permutations(torch.zeros(2, 8, dtype=torch.int64, device=cuda_device))
 
+
+
+@pytest.mark.parametrize("img_size,P,E,C,dt", [(28, 4, 48, 3, torch.float32), (32, 4, 512, 3, torch.float32),
+                                               (224, 16, 384, 3, torch.bfloat16), (224, 16, 64, 3, torch.float32),
+                                               (30, 4, 16, 1, torch.float32)])
+def test_patch_embed_kernels_match_reference_module(cuda_device, img_size, P, E, C, dt):
+    """SpectralPatchEmbed through csrc/embed.cu (patch gather + cast | GEMM | cls / position / dropout pass) against
+    the module's stock composition (unfold -> rfft2(ortho).real -> gains -> Linear -> cat -> + pos; spectre.py:124-156)
+    on the CPU: output and the gradients of all six parameters.  30x30 with P=4 exercises the crop to 28x28."""
+    from vit_spectre_experiments_b200.model import SpectralPatchEmbed
+
+    torch.manual_seed(img_size + E)
+    n = (img_size // P) ** 2
+    ref = SpectralPatchEmbed(E, P, n, 0.0, C)
+    with torch.no_grad():
+        ref.freq_weight_h.add_(0.3 * torch.randn(P))
+        ref.freq_weight_w.add_(0.3 * torch.randn(P // 2 + 1))
+    dev = SpectralPatchEmbed(E, P, n, 0.0, C)
+    dev.load_state_dict(ref.state_dict())
+    dev.to(cuda_device)
+    img = torch.randn(3, C, img_size, img_size)
+    w = torch.randn(3, n + 1, E)
+    y_ref = ref(img)                                   # CPU: the stock path
+    (y_ref * w).sum().backward()
+    bf = dt == torch.bfloat16
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=bf):
+        y = dev(img.to(cuda_device))
+    assert y.dtype == dt
+    (y.float() * w.to(cuda_device)).sum().backward()
+    tol = 2e-2 if bf else 2e-5
+    assert rel_err(y, y_ref) <= tol
+    for (k, pr), (_, pd) in zip(ref.named_parameters(), dev.named_parameters()):
+        assert pd.grad is not None and rel_err(pd.grad, pr.grad) <= (3e-2 if bf else 1e-4), k
+
+
+def test_patch_embed_dropout_consistent(cuda_device):
+    """Counter-based dropout of the embedding pass: keep-rate ~ 1 - p, kept values scaled by 1 / (1 - p), and the
+    backward recomputes the same mask (no gradient through dropped positions)."""
+    from vit_spectre_experiments_b200.functional import patch_embed
+
+    torch.manual_seed(2)
+    B, C, S, P, E = 16, 3, 32, 4, 64
+    n = (S // P) ** 2
+    img = torch.randn(B, C, S, S, device=cuda_device)
+    M = torch.randn(C * P * P, E, device=cuda_device, requires_grad=True)
+    bias = torch.randn(E, device=cuda_device, requires_grad=True)
+    cls = torch.randn(1, 1, E, device=cuda_device, requires_grad=True)
+    pos = torch.randn(1, n + 1, E, device=cuda_device, requires_grad=True)
+    y0 = patch_embed(img, M, bias, cls, pos, P, 0.0, 0)
+    y = patch_embed(img, M, bias, cls, pos, P, 0.2, 99)
+    kept = y != 0
+    assert abs(kept.float().mean().item() - 0.8) < 1e-2
+    assert torch.allclose(y[kept], y0[kept] / 0.8, rtol=1e-5, atol=1e-5)
+    assert torch.equal(y, patch_embed(img, M, bias, cls, pos, P, 0.2, 99))
+    (y * (~kept).float()).sum().backward()
+    assert pos.grad.abs().max().item() == 0.0 and M.grad.abs().max().item() == 0.0

@@ -27,6 +27,10 @@ EXPORTED_SYMBOLS = (
     "spectre_norm_act_bwd",
     "spectre_norm_act_bwd_workspace_bytes",
     "spectre_norm_act_supported",
+    "spectre_patch_gather",
+    "spectre_embed_finish_fwd",
+    "spectre_embed_finish_bwd",
+    "spectre_embed_finish_bwd_workspace_bytes",
     "spectre_permut_fwd",
     "spectre_permut_bwd",
     "spectre_debug_mark_main_kernel_end",
@@ -101,6 +105,14 @@ def load() -> ctypes.CDLL:
         lib.spectre_norm_act_bwd_workspace_bytes.restype = _sz
         lib.spectre_norm_act_supported.argtypes = [_i, _i, _i]
         lib.spectre_norm_act_supported.restype = _i
+        lib.spectre_patch_gather.argtypes = [_p, _p, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_patch_gather.restype = _i
+        lib.spectre_embed_finish_fwd.argtypes = [_p, _p, _p, _p, _i, _i, _i, _i, ctypes.c_float, ctypes.c_ulonglong, _p]
+        lib.spectre_embed_finish_fwd.restype = _i
+        lib.spectre_embed_finish_bwd.argtypes = [_p, _p, _p, _p, _sz, _i, _i, _i, _i, ctypes.c_float, ctypes.c_ulonglong, _p]
+        lib.spectre_embed_finish_bwd.restype = _i
+        lib.spectre_embed_finish_bwd_workspace_bytes.argtypes = [_i, _i, _i]
+        lib.spectre_embed_finish_bwd_workspace_bytes.restype = _sz
         lib.spectre_permut_fwd.argtypes = [_p, _p, _p, _p, _i, ctypes.c_longlong, _i, _i, _p]
         lib.spectre_permut_fwd.restype = _i
         lib.spectre_permut_bwd.argtypes = [_p, _p, _p, _p, _i, ctypes.c_longlong, _i, _i, _p]

@@ -229,6 +229,71 @@ def inverse_permutations(perms: torch.Tensor) -> torch.Tensor:
     return inv
 
 
+class _PatchEmbed(torch.autograd.Function):
+    """``dropout(cat(cls, patches @ M + b) + pos)`` (spectre.py:124-156 with the DFT / gains / projection folded into
+    ``M``): patch gather + cast, the library GEMM, and the cls / position / dropout pass -- three launches forward,
+    four backward (``spectre_patch_gather``, ``spectre_embed_finish_fwd/bwd``)."""
+
+    @staticmethod
+    def forward(ctx, img, M, bias, cls, pos, P, drop_p, seed, dt):
+        lib = _lib.load()
+        if not img.is_cuda:
+            raise RuntimeError("patch_embed: CUDA (sm_100a) only; there is no CPU fallback")
+        img = img.float().contiguous()
+        B, C, Hi, Wi = img.shape
+        nH, nW = Hi // P, Wi // P
+        n, K, E = nH * nW, C * P * P, M.shape[1]
+        code = _DTYPE_CODE[dt]
+        A = torch.empty(B * n, K, dtype=dt, device=img.device)
+        st = _stream_ptr(img.device)
+        with torch.cuda.device(img.device):
+            with _timed("patch_gather", (B * n, K, A.element_size(), img.numel() * 4 + A.numel() * A.element_size())):
+                rc = lib.spectre_patch_gather(img.data_ptr(), A.data_ptr(), B, C, Hi, Wi, P, code, st)
+            _lib.check(rc, "spectre_patch_gather")
+            _lib.count_launches()
+            Md = M.detach().to(dt)
+            tok = torch.addmm(bias.detach().to(dt), A, Md)
+            out = torch.empty(B, n + 1, E, dtype=dt, device=img.device)
+            clsf, posf = cls.detach().float().contiguous().view(-1), pos.detach().float().contiguous().view(n + 1, E)
+            with _timed("embed_finish_fwd", (B * (n + 1), E, out.element_size(), (tok.numel() + out.numel()) * out.element_size())):
+                rc = lib.spectre_embed_finish_fwd(tok.data_ptr(), clsf.data_ptr(), posf.data_ptr(), out.data_ptr(), B, n + 1, E,
+                                                  code, float(drop_p), int(seed), st)
+            _lib.check(rc, "spectre_embed_finish_fwd")
+            _lib.count_launches()
+        ctx.save_for_backward(A, Md)
+        ctx.meta = (B, n, E, float(drop_p), int(seed), code, M.dtype, bias.dtype, cls.shape, pos.shape, cls.dtype, pos.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _lib.load()
+        A, Md = ctx.saved_tensors
+        B, n, E, drop_p, seed, code, m_dt, b_dt, cls_shape, pos_shape, cls_dt, pos_dt = ctx.meta
+        dout = dout.to(A.dtype).contiguous()
+        dtok = torch.empty(B * n, E, dtype=A.dtype, device=A.device)
+        dpos = torch.empty(n + 1, E, dtype=torch.float32, device=A.device)
+        with torch.cuda.device(A.device):
+            nws = lib.spectre_embed_finish_bwd_workspace_bytes(B, n + 1, E)
+            ws = torch.empty(max(nws, 16), dtype=torch.uint8, device=A.device)
+            with _timed("embed_finish_bwd", (B * (n + 1), E, dout.element_size(), (dout.numel() + dtok.numel()) * dout.element_size())):
+                rc = lib.spectre_embed_finish_bwd(dout.data_ptr(), dtok.data_ptr(), dpos.data_ptr(), ws.data_ptr(), nws, B, n + 1, E,
+                                                  code, drop_p, seed, _stream_ptr(A.device))
+            _lib.check(rc, "spectre_embed_finish_bwd")
+            _lib.count_launches()
+        dM = torch.mm(A.t(), dtok).to(m_dt)
+        dbias = dpos[1:].sum(0).to(b_dt)
+        return (None, dM, dbias, dpos[0].reshape(cls_shape).to(cls_dt), dpos.reshape(pos_shape).to(pos_dt),
+                None, None, None, None)
+
+
+def patch_embed(img, M, bias, cls, pos, patch: int, drop_p: float = 0.0, seed: int = 0, dtype=torch.float32) -> torch.Tensor:
+    """``dropout(cat(cls, patches(img) @ M + bias) + pos)`` -> ``[B, 1 + n, E]`` in ``dtype`` (float32 / bfloat16).
+
+    img float32 ``[B, C, Hi, Wi]``; ``M [C*P*P, E]`` the folded Re(rfft2) x gains x projection matrix (rows ordered
+    (c, i, j)); cls ``[1, 1, E]``, pos ``[1, 1 + n, E]``.  Gradients flow to ``M``, ``bias``, ``cls`` and ``pos``."""
+    return _PatchEmbed.apply(img, M, bias, cls, pos, int(patch), float(drop_p), int(seed), dtype)
+
+
 def fft_mix(x: torch.Tensor, filt: torch.Tensor, grid, has_cls: bool = True) -> torch.Tensor:
     """``cat(cls, irfft2(rfft2(x_grid, ortho) * filt, ortho))`` in one fused CUDA pass.
 

@@ -279,6 +279,13 @@ class SpectralPatchEmbed(nn.Module):
             M = torch.matmul(self._cos_dft(img.device), wf.view(self.embed_dim, chans, P * half).permute(1, 2, 0))
             M = M.reshape(chans * P * P, self.embed_dim)
         dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else img.dtype
+        if (dt in (torch.float32, torch.bfloat16) and P % 4 == 0 and img.shape[3] % 4 == 0 and self.embed_dim % 8 == 0):
+            # patch gather + cast | GEMM | cls / position / dropout pass: the CUDA kernels of csrc/embed.cu
+            from .functional import patch_embed
+
+            p = self.dropout.p if self.training else 0.0
+            return patch_embed(img, M, self.proj.bias, self.cls_token, self.position_embeddings, P, p,
+                               _dropout_seed() if p > 0 else 0, dt)
         patches = img[:, :, :nh * P, :nw * P].reshape(batch, chans, nh, P, nw, P).permute(0, 2, 4, 1, 3, 5)
         flat = patches.to(dt).reshape(batch * nh * nw, chans * P * P)        # one gather copy (+ cast)
         tokens = torch.addmm(self.proj.bias.to(dt), flat, M.to(dt)).view(batch, nh * nw, self.embed_dim)
