@@ -1,6 +1,7 @@
 // extern "C" entry points declared in include/spectre_b200.h: argument validation,
 // error bookkeeping, dispatch to the templated launchers.  No torch types here.
 #include <cstdarg>
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -48,6 +49,14 @@ int device_sm_count() {
 }
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("SB200_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 cudaError_t ensure_dynamic_smem(const void* kernel, int bytes) {
   static std::mutex mu;
   static std::unordered_map<const void*, unsigned long long> done[2];   // bit d (of word d / 64) = device d configured
@@ -69,6 +78,8 @@ cudaError_t ensure_dynamic_smem(const void* kernel, int bytes) {
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const float4* __restrict__ part, float4* __restrict__ out,
                                                               size_t n4, int slabs) {
   __shared__ float4 sm[4][64];
+  pdl_launch_dependents();
+  pdl_wait();
   const int col = threadIdx.x & 63, ln = threadIdx.x >> 6;
   const size_t i = static_cast<size_t>(blockIdx.x) * 64 + col;
   float4 a[4];
@@ -108,8 +119,8 @@ void launch_reduce_partials(const float* part, float* out, size_t n_floats, int 
   }
   const size_t n4 = n_floats / 4;
   const unsigned blocks = static_cast<unsigned>((n4 + 63) / 64);
-  reduce_partials_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(part),
-                                                     reinterpret_cast<float4*>(out), n4, slabs);
+  launch_pdl(reduce_partials_kernel, dim3(blocks), dim3(256), 0, stream, reinterpret_cast<const float4*>(part),
+             reinterpret_cast<float4*>(out), n4, slabs);
 }
 
 static int check_common(const char* fn, int B, int H, int W, int E, int has_cls, int dtype) {

@@ -23,6 +23,32 @@ bool aligned16(const void* p);
 // (kernel, current device) -- a process driving several GPUs must not rely on a once-per-process flag.
 cudaError_t ensure_dynamic_smem(const void* kernel, int bytes);
 
+// ------------------------------------------------------------------ programmatic dependent launch
+// Every kernel here is enqueued with cudaLaunchAttributeProgrammaticStreamSerialization (launch_pdl) and runs
+//   pdl_launch_dependents();   as its first statement: the next kernel of the stream may be scheduled as soon as SMs
+//                              free up, so its launch latency and its prologue (barrier init, TMEM allocation, filter /
+//                              DFT-matrix staging) overlap this kernel's tail;
+//   pdl_wait();                before its first access to memory a predecessor may still be writing (or reading, for
+//                              buffers it overwrites): blocks until the preceding grid has completed and flushed.
+// Launched without the attribute (SB200_PDL=0, or by a caller using <<<>>>) both are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ------------------------------------------------------------------ channel-pair I/O
 // One thread moves two adjacent channels: a 64-bit access for fp32, a 32-bit
 // access for bf16.  Activations are touched exactly once, so loads/stores use the

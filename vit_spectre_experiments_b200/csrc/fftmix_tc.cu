@@ -214,6 +214,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
   __shared__ __align__(16) uint8_t sDummy[8 * 16];   // sink for the padded rows of stmatrix
 
   const long long t_start = clock64();
+  pdl_launch_dependents();
   SB200_WALL(0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ct = blockIdx.x % p.nct;
@@ -233,6 +234,7 @@ fftmix_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     for (int k = 0; k < 16; ++k) mbar_init(&dready_bar[k >> 2][k & 3], 1);
     mbar_fence_init();
     // prologue loads: fill the input ring before the CTA-wide setup barrier (only the barriers are needed)
+    pdl_wait();   // x is the preceding kernel's output; everything else in the setup is independent of it
     const uint32_t bytes0 = (half1 ? 2u : 1u) * C::HW * 128u;
     for (int it = 0; it < S && it < ntiles; ++it) {
       uint8_t* dst = smem + it * C::kStageBytes;
@@ -663,7 +665,7 @@ static int fwd_launch(const void* x, const float* filt, void* y, int B, int E, i
   p.B = B; p.E = E; p.cls = cls;
   p.prof = g_prof;
   plan_grid(B, E, &p.nct, &p.img_stride);
-  kern<<<p.nct * p.img_stride, kThreads, SM::kBytes, st>>>(tmx, tmy, p);
+  launch_pdl(kern, dim3(p.nct * p.img_stride), dim3(kThreads), SM::kBytes, st, tmx, tmy, p);
   last_launch_count() = 1;
   const cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "fftmix_tc_fwd launch: %s", cudaGetErrorString(err));
@@ -747,6 +749,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
   __shared__ __align__(16) uint8_t sDummy[8 * 16];
 
   const long long t_start = clock64();
+  pdl_launch_dependents();
   SB200_WALL(0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int cb = blockIdx.x % p.nblk;
@@ -767,6 +770,7 @@ fftmix_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_c
     for (int s = 0; s < 2; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int k = 0; k < 24; ++k) mbar_init(&dready_bar[k >> 2][k & 3], 1);
     mbar_fence_init();
+    pdl_wait();   // dy is the preceding kernel's output; everything else in the setup is independent of it
     if (ntiles > 0) {   // prologue: first tile's dy and x
       const int b0 = 2 * (pair0 + (ntiles - 1) * p.pair_stride);   // first tile in the (descending) sweep
       const bool two = b0 + 1 < p.B;
@@ -1223,7 +1227,7 @@ static int bwd_launch(const void* dy, const void* x, const float* filt, void* dx
   p.part = p.pair_stride > 1 ? static_cast<float*>(ws) : dfilt;
   p.B = B; p.E = E; p.cls = cls;
   p.prof = g_prof;
-  kern<<<p.nblk * p.pair_stride, kThreads, SM::kBytes, st>>>(tmdy, tmx, tmdx, p);
+  launch_pdl(kern, dim3(p.nblk * p.pair_stride), dim3(kThreads), SM::kBytes, st, tmdy, tmx, tmdx, p);
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "fftmix_tc_bwd launch: %s", cudaGetErrorString(err));
   last_launch_count() = 1;

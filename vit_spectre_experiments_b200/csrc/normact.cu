@@ -581,6 +581,8 @@ __global__ void __launch_bounds__(256) reduce_gamma_beta_kernel(const float* __r
                                                                 float* __restrict__ dbeta, float* __restrict__ dsum, int N,
                                                                 int nacc, int slabs) {
   __shared__ float sm[32][9];
+  pdl_launch_dependents();
+  pdl_wait();
   const int c8 = threadIdx.x & 7, ln = threadIdx.x >> 3;
   const int col = blockIdx.x * 8 + c8;
   const int ncol = nacc * N;
@@ -829,7 +831,8 @@ int spectre_norm_act_bwd(const spectre_norm_act_t* d, void* stream) {
     int rc = SPECTRE_OK, fgrid = 0;
     if (fast_bwd_launch(a, d->workspace ? d->workspace_bytes : 0, st, &rc, &fgrid)) {
       if (rc != SPECTRE_OK) return rc;
-      reduce_gamma_beta_kernel<<<(a.nacc * a.N + 7) / 8, 256, 0, st>>>(a.part, d->dgamma, d->dbeta, d->dcolsum, a.N, a.nacc, fgrid);
+      launch_pdl(reduce_gamma_beta_kernel, dim3((a.nacc * a.N + 7) / 8), dim3(256), 0, st, static_cast<const float*>(a.part),
+                 d->dgamma, d->dbeta, d->dcolsum, a.N, a.nacc, fgrid);
       last_launch_count() = 2;
       const cudaError_t err = cudaGetLastError();
       if (err != cudaSuccess) return fail(SPECTRE_E_CUDA, "norm_act_bwd launch: %s", cudaGetErrorString(err));

@@ -54,11 +54,14 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
     if (has_d2) bulk_load(st + off_d2, static_cast<const __nv_bfloat16*>(a.dout2) + row0 * N, bmain, bar);
     if (has_dp) bulk_load(st + off_dp, static_cast<const __nv_bfloat16*>(a.d_out_pool) + row0 * (N / 4), bpool, bar);
   };
+  pdl_launch_dependents();
   if (threadIdx.x == 0) {
     for (int k = 0; k < S; ++k) ptx::mbar_init(&full[k], 1);
     ptx::mbar_fence_init();
-    for (int it = 0; it < S - 1 && it < n_it; ++it) issue(it, it);
   }
+  pdl_wait();   // nothing above touches global memory
+  if (threadIdx.x == 0)
+    for (int it = 0; it < S - 1 && it < n_it; ++it) issue(it, it);
   for (int i = threadIdx.x; i < N; i += NT) {
     sgb[i] = a.gamma[i];
     sgb[N + i] = a.beta[i];
@@ -292,7 +295,7 @@ bool fast_bwd_launch(const Args& a0, size_t workspace_bytes, cudaStream_t st, in
     *rc = fail(SPECTRE_E_CUDA, "norm_act_bwd: cudaFuncSetAttribute failed");
     return true;
   }
-  fn<<<grid, threads, smem, st>>>(a);
+  launch_pdl(fn, dim3(grid), dim3(threads), smem, st, a);
   const cudaError_t err = cudaGetLastError();
   *rc = err == cudaSuccess ? SPECTRE_OK : fail(SPECTRE_E_CUDA, "norm_act_bwd (fast) launch: %s", cudaGetErrorString(err));
   *grid_out = grid;

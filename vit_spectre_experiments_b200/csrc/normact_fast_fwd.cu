@@ -51,11 +51,14 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
     if (has_in1) bulk_load(st + off_in1, static_cast<const __nv_bfloat16*>(a.in1) + row0 * N, bmain, bar);
     if (MODE != kSkipNone) bulk_load(st + off_skip, static_cast<const __nv_bfloat16*>(a.skip) + row0 * NS, bskip, bar);
   };
+  pdl_launch_dependents();
   if (threadIdx.x == 0) {
     for (int k = 0; k < S; ++k) ptx::mbar_init(&full[k], 1);
     ptx::mbar_fence_init();
-    for (int it = 0; it < S - 1 && it < n_it; ++it) issue(it, it);
   }
+  pdl_wait();   // nothing above touches global memory
+  if (threadIdx.x == 0)
+    for (int it = 0; it < S - 1 && it < n_it; ++it) issue(it, it);
   __syncthreads();
 
   const u64 c0 = splat(kGeluC0), c1 = splat(kGeluC1), c2 = splat(kGeluC2), half2 = splat(0.5f);
@@ -217,7 +220,7 @@ bool fast_fwd_launch(const Args& a0, cudaStream_t st, int* rc) {
   const long long groups = (a.rows + rpc - 1) / rpc;
   const long long cap = static_cast<long long>(device_sm_count()) * 2;
   const int grid = static_cast<int>(groups < cap ? groups : cap);
-  fn<<<grid, threads, smem, st>>>(a);
+  launch_pdl(fn, dim3(grid), dim3(threads), smem, st, a);
   const cudaError_t err = cudaGetLastError();
   *rc = err == cudaSuccess ? SPECTRE_OK : fail(SPECTRE_E_CUDA, "norm_act_fwd (fast) launch: %s", cudaGetErrorString(err));
   return true;
