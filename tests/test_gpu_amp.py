@@ -114,3 +114,36 @@ def test_two_devices_same_process(cuda_device):
         y = norm_act(y, torch.ones(384, device=d), torch.zeros(384, device=d), skip=x)
         outs.append(y.cpu())
     assert torch.equal(outs[0], outs[1])
+
+
+@pytest.mark.parametrize("T,E", [(65, 512), (197, 384), (50, 48)])
+def test_fnet_and_fft_module_on_gpu(cuda_device, T, E):
+    """``fft_bare`` (orthogonal_permut.py:23-28) and ``modules.FFT`` (modules/spectre.py:5-14) on the GPU: the constant-DFT
+    GEMMs against ``torch.fft`` (cuFFT) on the same device, forward and input gradient; fp32 <= 1e-5 of max|ref|
+    (full-fp32 GEMMs, TF32 left untouched for the caller), bf16 under autocast <= 3e-2."""
+    from vit_spectre_experiments_b200 import FFT, FNetMix
+
+    torch.manual_seed(T + E)
+    tf32 = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True           # the reference enables it (repl/train.py:36-39)
+    try:
+        x = torch.randn(6, T, E, device=cuda_device, requires_grad=True)
+        w = torch.randn(6, T, E, device=cuda_device)
+        m = FNetMix(E, T, 4, E).to(cuda_device)
+        y = m(x)
+        ref = torch.fft.fft2(x, dim=(-2, -1)).real
+        assert rel_err(y, ref) <= 1e-5
+        (gy,) = torch.autograd.grad((y * w).sum(), x)
+        (gr,) = torch.autograd.grad((ref * w).sum(), x)
+        assert rel_err(gy, gr) <= 1e-5
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            yb = m(x)
+        assert yb.dtype == torch.bfloat16 and rel_err(yb, ref) <= 3e-2
+        f = FFT()
+        assert rel_err(f(x), torch.fft.rfft(x, dim=-1).real) <= 1e-5
+        assert torch.backends.cuda.matmul.allow_tf32 is True
+        # the constant matrices are uploaded once per (device, dtype), not per call
+        a = m._dft("e", x)
+        assert m._dft("e", x) is a
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = tf32

@@ -205,3 +205,25 @@ def test_mixer_construction_validates_grid_and_widths():
     assert lib.spectre_norm_act_supported(384, 1536, 1) == 1 and lib.spectre_norm_act_supported(1536, 384, 0) == 1
     assert lib.spectre_norm_act_supported(5120, 5120, 0) == 0 and lib.spectre_norm_act_supported(12, 12, 0) == 0
     assert lib.spectre_norm_act_supported(512, 768, 1) == 1 and lib.spectre_norm_act_supported(48, 256, 0) == 1
+
+
+def test_fft_module_matches_reference_golden():
+    """``modules.FFT`` (spectre_vit/modules/spectre.py:5-14: ``rfft(x, dim=-1).real``) as a constant cosine-DFT GEMM
+    reproduces the output the REFERENCE's own module produced (tests/golden/ref_fft_module.npz) and torch.fft."""
+    import numpy as np
+
+    from vit_spectre_experiments_b200 import FFT
+
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_fft_module.npz"))
+    m = FFT()
+    assert len(m.state_dict()) == 0
+    out = m(torch.from_numpy(g["x"]))
+    assert out.shape == g["out"].shape and np.abs(out.numpy() - g["out"]).max() < 2e-6
+    x = torch.randn(4, 9, 50, dtype=torch.float64, requires_grad=True)
+    y = m(x)
+    ref = torch.fft.rfft(x, dim=-1).real
+    assert (y - ref).abs().max().item() < 1e-12
+    w = torch.randn_like(ref)
+    (gy,) = torch.autograd.grad((y * w).sum(), x)
+    (gr,) = torch.autograd.grad((ref * w).sum(), x)
+    assert (gy - gr).abs().max().item() < 1e-12

@@ -157,39 +157,96 @@ class HaarDWTMix(_Fp32ParamMixin, nn.Module):
         return f"embed_dim={self.embed_dim}, grid={self.grid}, has_cls={self.has_cls}"
 
 
-class FNetMix(nn.Module):
+def _cos_sin(n: int):
+    """float64 ``cos`` / ``sin`` of ``2 pi j k / n`` with the angle reduced exactly (integer ``j k mod n``)."""
+    k = torch.arange(n, dtype=torch.int64)
+    ang = (2.0 * math.pi / n) * ((k[:, None] * k[None, :]) % n).to(torch.float64)
+    return torch.cos(ang), torch.sin(ang)
+
+
+class _DftBuffers:
+    """Constant DFT matrices kept as float64 masters on the CPU and cached per (device, dtype): the cast / upload happens
+    once, not on every forward, and nothing is added to ``state_dict()``."""
+
+    def _dft(self, name: str, like: torch.Tensor) -> torch.Tensor:
+        cache = self.__dict__.setdefault("_dft_cache", {})
+        key = (name, like.device, like.dtype)
+        m = cache.get(key)
+        if m is None:
+            m = cache[key] = self._dft_master[name].to(device=like.device, dtype=like.dtype)
+        return m
+
+    def __deepcopy__(self, memo):      # _get_clones deep-copies the layer: share the masters, drop the device cache
+        import copy
+
+        new = self.__class__.__new__(self.__class__)
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            if k == "_dft_cache":
+                continue
+            new.__dict__[k] = v if k == "_dft_master" else copy.deepcopy(v, memo)
+        return new
+
+
+def _matmul_exact(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """fp32 operands multiply in full fp32 (the reference's ``torch.fft`` is fp32-exact; TF32 would cost 1e-3)."""
+    if a.dtype == torch.float32 and a.is_cuda and torch.backends.cuda.matmul.allow_tf32:
+        torch.backends.cuda.matmul.allow_tf32 = False
+        try:
+            return torch.matmul(a, b)
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = True
+    return torch.matmul(a, b)
+
+
+class FFT(_DftBuffers, nn.Module):
+    """``torch.fft.rfft(x, dim=-1).real`` (``spectre_vit/modules/spectre.py:5-14``): ``[..., E] -> [..., E//2 + 1]``.
+
+    The real part of the real DFT is one dense cosine matrix, ``x @ C`` with ``C[e, k] = cos(2 pi e k / E)``: GEMM-shaped,
+    so it is a library GEMM against a constant (no cuFFT plan, no complex intermediate, differentiable through
+    ``matmul``); fp32 inputs multiply in full fp32.  Parameter-free, as the reference module."""
+
+    def __init__(self) -> None:
+        super().__init__()
+        self._dft_master = {}
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        E = x.shape[-1]
+        name = f"rfft_cos_{E}"
+        if name not in self._dft_master:
+            self._dft_master[name] = _cos_sin(E)[0][:, : E // 2 + 1].contiguous()
+        dt = x.dtype if x.dtype in (torch.float32, torch.float64, torch.bfloat16, torch.float16) else torch.float32
+        return _matmul_exact(x.to(dt), self._dft(name, x.to(dt)))
+
+
+class FNetMix(_DftBuffers, nn.Module):
     """``fft_bare`` (FNet): ``Re(fft2(x, dim=(-2, -1)))`` over (tokens, channels), parameter-free
     (``spectre_vit/repl/orthogonal_permut.py:23-28``; mode name ``spectre.py:31``).
 
     ``Re(F_T x F_E) = C_T x C_E - S_T x S_E`` with the cosine / sine DFT matrices, i.e. two dense real GEMMs
     ``x @ [C_E | S_E]`` and ``[C_T | -S_T] @ [xC ; xS]``: GEMM-shaped work, left to the library GEMM (cuBLAS) --
-    no custom kernel, no complex intermediates, and it runs in the activation dtype under autocast.  The
-    matrices are non-persistent buffers: the module adds nothing to ``state_dict()``.
-    """
+    no custom kernel, no complex intermediates, and it runs in the activation dtype under autocast (fp32 inputs in
+    full fp32).  The matrices are float64 masters cached per (device, dtype): nothing is added to ``state_dict()``
+    and no conversion runs per forward."""
 
     def __init__(self, embed_dim: int, token_dim: int, num_heads: int, out_channels: int):
         super().__init__()
         if out_channels != embed_dim:
             raise ValueError("FNetMix keeps the channel count: out_channels must equal embed_dim")
         self.embed_dim, self.token_dim, self.num_heads = embed_dim, token_dim, num_heads
-
-        def cos_sin(n):
-            k = torch.arange(n, dtype=torch.int64)
-            ang = (2.0 * math.pi / n) * ((k[:, None] * k[None, :]) % n).to(torch.float64)
-            return torch.cos(ang), torch.sin(ang)
-
-        ce, se = cos_sin(embed_dim)
-        ct, st = cos_sin(token_dim)
-        self.register_buffer("dft_e", torch.cat([ce, se], dim=1), persistent=False)     # [E, 2E], float64 master
-        self.register_buffer("dft_t", torch.cat([ct, -st], dim=1), persistent=False)    # [T, 2T]
+        ce, se = _cos_sin(embed_dim)
+        ct, st = _cos_sin(token_dim)
+        self._dft_master = {"e": torch.cat([ce, se], dim=1), "t": torch.cat([ct, -st], dim=1)}   # [E, 2E], [T, 2T]
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.dim() != 3 or x.shape[1] != self.token_dim or x.shape[2] != self.embed_dim:
             raise ValueError(f"FNetMix expects [B, {self.token_dim}, {self.embed_dim}], got {tuple(x.shape)}")
         E = self.embed_dim
-        xe = torch.matmul(x, self.dft_e.to(x.dtype))                   # [B, T, 2E] = [x C_E | x S_E]
+        if torch.is_autocast_enabled(x.device.type):
+            x = x.to(torch.get_autocast_dtype(x.device.type))
+        xe = _matmul_exact(x, self._dft("e", x))                       # [B, T, 2E] = [x C_E | x S_E]
         stacked = torch.cat([xe[..., :E], xe[..., E:]], dim=1)         # [B, 2T, E]
-        return torch.matmul(self.dft_t.to(x.dtype), stacked)           # C_T (x C_E) - S_T (x S_E)
+        return _matmul_exact(self._dft("t", x), stacked)               # C_T (x C_E) - S_T (x S_E)
 
     def extra_repr(self) -> str:
         return f"embed_dim={self.embed_dim}, token_dim={self.token_dim}"
