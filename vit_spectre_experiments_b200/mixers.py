@@ -188,15 +188,43 @@ class _DftBuffers:
         return new
 
 
-def _matmul_exact(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
-    """fp32 operands multiply in full fp32 (the reference's ``torch.fft`` is fp32-exact; TF32 would cost 1e-3)."""
-    if a.dtype == torch.float32 and a.is_cuda and torch.backends.cuda.matmul.allow_tf32:
+class _NoTF32:
+    """fp32 GEMMs in full fp32 inside the block (the reference's ``torch.fft`` is fp32-exact; TF32 would cost 1e-3),
+    whatever the caller's ``allow_tf32`` (the reference enables it, repl/train.py:36-39); restored on exit."""
+
+    def __enter__(self):
+        self.prev = torch.backends.cuda.matmul.allow_tf32
         torch.backends.cuda.matmul.allow_tf32 = False
-        try:
-            return torch.matmul(a, b)
-        finally:
-            torch.backends.cuda.matmul.allow_tf32 = True
-    return torch.matmul(a, b)
+
+    def __exit__(self, *exc):
+        torch.backends.cuda.matmul.allow_tf32 = self.prev
+        return False
+
+
+class _ConstMatmul(torch.autograd.Function):
+    """``x @ c`` (``left=False``) or ``c @ x`` (``left=True``) against a constant matrix ``c``, forward AND backward in
+    full fp32 for fp32 operands (autograd would run the backward GEMM later, under the caller's TF32 setting)."""
+
+    @staticmethod
+    def forward(ctx, x, c, left):
+        ctx.save_for_backward(c)
+        ctx.left = left
+        with _NoTF32():
+            return torch.matmul(c, x) if left else torch.matmul(x, c)
+
+    @staticmethod
+    def backward(ctx, g):
+        (c,) = ctx.saved_tensors
+        with _NoTF32():
+            gx = torch.matmul(c.transpose(-1, -2), g) if ctx.left else torch.matmul(g, c.transpose(-1, -2))
+        return gx, None, None
+
+
+def _matmul_exact(a: torch.Tensor, b: torch.Tensor, const_left: bool = False) -> torch.Tensor:
+    """``a @ b`` where one operand is a constant DFT matrix (``b``, or ``a`` with ``const_left``)."""
+    if const_left:
+        return _ConstMatmul.apply(b, a, True)
+    return _ConstMatmul.apply(a, b, False)
 
 
 class FFT(_DftBuffers, nn.Module):
@@ -246,7 +274,7 @@ class FNetMix(_DftBuffers, nn.Module):
             x = x.to(torch.get_autocast_dtype(x.device.type))
         xe = _matmul_exact(x, self._dft("e", x))                       # [B, T, 2E] = [x C_E | x S_E]
         stacked = torch.cat([xe[..., :E], xe[..., E:]], dim=1)         # [B, 2T, E]
-        return _matmul_exact(self._dft("t", x), stacked)               # C_T (x C_E) - S_T (x S_E)
+        return _matmul_exact(self._dft("t", x), stacked, const_left=True)   # C_T (x C_E) - S_T (x S_E)
 
     def extra_repr(self) -> str:
         return f"embed_dim={self.embed_dim}, token_dim={self.token_dim}"
