@@ -181,6 +181,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cuda-graph", action="store_true",
+                    help="capture the whole step (fwd, bwd, gradient all-reduce, AdamW) in one CUDA graph and replay it")
     args = ap.parse_args()
 
     from vit_spectre_experiments_b200.configs import load_named
@@ -234,7 +236,8 @@ def main():
             config["teacher"] = "reference DinoClassifier(dinov3_vitb16(pretrained=False)) from baseline/_ref, frozen"
         else:
             config["teacher"] = "stock ViT-B/16 of the same sizes (baseline/_ref absent: run baseline/install_ref.sh)"
-    tr = Trainer(cfg, dev, teacher=teacher)
+    tr = Trainer(cfg, dev, teacher=teacher, cuda_graph=args.cuda_graph)
+    config["cuda_graph"] = bool(args.cuda_graph)
     img, lab = tr.synthetic_batch(batch, rank)
     warm = max(3, args.warmup)
     K = args.steps
@@ -250,7 +253,7 @@ def main():
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     TIMER.reset()
-    TIMER.enabled = True
+    TIMER.enabled = not args.cuda_graph      # events cannot be recorded inside a replayed graph: see below
     launches0 = _lib.launch_counter["kernels"]
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
@@ -262,6 +265,14 @@ def main():
     ms_total = t0.elapsed_time(t1)
     launches = _lib.launch_counter["kernels"] - launches0
     clocks = sampler.stop() if sampler else None
+    if args.cuda_graph:
+        # per-kernel timings for the roofline block: the same step run eagerly (same kernels, same shapes) right after
+        # the timed graph replays, bracketed by CUDA events on the launching stream
+        TIMER.enabled = True
+        for _ in range(min(K, 5)):
+            tr._eager_step(img, lab)
+        TIMER.enabled = False
+        config["roofline_timing"] = "eager pass after the timed graph replays"
     ksum = TIMER.summary()
     final_loss = float(loss.item())
 
@@ -341,7 +352,7 @@ def main():
         nparam = sum(p.numel() for p in tr.model.parameters())
         hid, P, Cin = cfg.hidden_dim, cfg.patch_size, cfg.in_channels
         gemm_flops_img = 3 * 2 * (L * 2 * T * E * hid + (T - 1) * Cin * P * P * E + E * cfg.num_classes)
-        own_bytes_step = sum(k["algo_bytes"] * k["launches"] for k in kernels.values()) / K
+        own_bytes_step = sum(k["algo_bytes"] * k["launches"] for k in kernels.values()) / (min(K, 5) if args.cuda_graph else K)
         mem_bytes_step = own_bytes_step + batch * Cin * cfg.img_size ** 2 * 4 + nparam * 28
         tf_peak = peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1395.1))
         if cfg.precision != "bf16":

@@ -117,6 +117,10 @@ typedef struct spectre_norm_act_t {
    * N / pool_k columns per row instead of N.  Backward: d_out_pool [rows, N / pool_k] is the gradient that arrived
    * through out_pool; it is added as d_out_pool[r, j / pool_k] / pool_k to dout[r, j].  NULL = unused. */
   void* out_pool; const void* d_out_pool; int pool_k;
+  /* Optional device word added (times an odd constant) to `seed` inside the kernel.  A step captured in a CUDA graph
+   * freezes the host-side seed; the graph bumps this word between replays so every replay draws a fresh mask, and the
+   * backward of the same replay reads the same value.  NULL = unused. */
+  const unsigned long long* seed_dev;
 } spectre_norm_act_t;
 
 int spectre_norm_act_fwd(const spectre_norm_act_t* desc, void* stream);
@@ -165,12 +169,15 @@ int spectre_permut_bwd(const void* dout, const long long* inv_perms, const float
  *   (counter-based, as in spectre_norm_act_fwd).  tok [B, T-1, E] and out [B, T, E] in act_dtype, cls [E], pos [T, E] fp32.
  * spectre_embed_finish_bwd: dtok[b, i] = mask * dout[b, 1 + i] / (1 - p);  dpos[t] = sum_b mask * dout[b, t] / (1 - p)
  *   (fully overwritten; d cls = dpos[0], d bias of the projection = sum_{t >= 1} dpos[t]).  workspace >=
- *   spectre_embed_finish_bwd_workspace_bytes(B, T, E): per-slab partials, summed in a fixed order. */
+ *   spectre_embed_finish_bwd_workspace_bytes(B, T, E): per-slab partials, summed in a fixed order.
+ *   seed_dev: optional device word added to the seed (see spectre_norm_act_t.seed_dev); NULL = unused. */
 int spectre_patch_gather(const float* img, void* out, int B, int C, int Hi, int Wi, int P, int act_dtype, void* stream);
 int spectre_embed_finish_fwd(const void* tok, const float* cls, const float* pos, void* out, int B, int T, int E,
-                             int act_dtype, float drop_p, unsigned long long seed, void* stream);
+                             int act_dtype, float drop_p, unsigned long long seed, const unsigned long long* seed_dev,
+                             void* stream);
 int spectre_embed_finish_bwd(const void* dout, void* dtok, float* dpos, void* workspace, size_t workspace_bytes,
-                             int B, int T, int E, int act_dtype, float drop_p, unsigned long long seed, void* stream);
+                             int B, int T, int E, int act_dtype, float drop_p, unsigned long long seed,
+                             const unsigned long long* seed_dev, void* stream);
 size_t spectre_embed_finish_bwd_workspace_bytes(int B, int T, int E);
 
 /* Measurement hook (bench.py's per-kernel roofline): the next backward mixer call on this thread records `event`

@@ -410,3 +410,56 @@ def test_patch_embed_dropout_consistent(cuda_device):
     assert torch.equal(y, patch_embed(img, M, bias, cls, pos, P, 0.2, 99))
     (y * (~kept).float()).sum().backward()
     assert pos.grad.abs().max().item() == 0.0 and M.grad.abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("mixer,precision", [("fft", "bf16"), ("dwt", "bf16"), ("fft", "fp32")])
+def test_training_step_is_cuda_graph_capturable(cuda_device, mixer, precision):
+    """include/spectre_b200.h promises that every entry point only enqueues work on the given stream: the WHOLE step
+    (forward, loss, backward with the fused parameter-gradient reductions, AdamW) is captured in one CUDA graph by
+    ``Trainer(cuda_graph=True)`` and replayed.  A replay from the same state is bit-identical; against the eager step
+    it agrees to rounding; with dropout on, every replay draws a fresh mask through the device-resident seed word."""
+    import copy
+    from types import SimpleNamespace
+
+    from vit_spectre_experiments_b200.train import Trainer
+
+    def cfg(p):
+        return SimpleNamespace(img_size=32, patch_size=4, in_channels=3, num_classes=10, embed_dim=64, num_encoders=2,
+                               num_heads=4, hidden_dim=256, dropout=p, activation="gelu", mixer=mixer, precision=precision,
+                               random_seed=42, learning_rate=1e-3, adam_betas=(0.9, 0.999), adam_weight_decay=0.01)
+
+    tg = Trainer(cfg(0.0), cuda_device, cuda_graph=True)
+    img, lab = tg.synthetic_batch(32)
+    tg.step(img, lab)                                   # 3 eager warm-up steps + capture + first replay
+    state = (copy.deepcopy(tg.model.state_dict()), copy.deepcopy(tg.opt.state_dict()))
+
+    def replay_from_state():
+        tg.model.load_state_dict(state[0])
+        tg.opt.load_state_dict(copy.deepcopy(state[1]))
+        loss = tg.step(img, lab).clone()
+        return loss, [p.detach().clone() for p in tg.model.parameters()]
+
+    la, pa = replay_from_state()
+    lb, pb = replay_from_state()
+    assert torch.equal(la, lb) and all(torch.equal(u, v) for u, v in zip(pa, pb))
+    # the same step, eagerly, from the same state
+    tg.model.load_state_dict(state[0])
+    tg.opt.load_state_dict(copy.deepcopy(state[1]))
+    le = tg._eager_step(img, lab)
+    assert abs(le.item() - la.item()) <= 1e-5 * abs(la.item()) + 1e-6
+    for u, v in zip(pa, tg.model.parameters()):
+        assert rel_err(u, v) <= (2e-2 if precision == "bf16" else 1e-4)
+    losses = [tg.step(img, lab).item() for _ in range(8)]
+    assert losses[-1] < losses[0]
+    # dropout inside a graph: fresh masks per replay
+    td = Trainer(cfg(0.3), cuda_device, cuda_graph=True)
+    td.step(img, lab)
+    st = (copy.deepcopy(td.model.state_dict()), copy.deepcopy(td.opt.state_dict()))
+    ls = []
+    for _ in range(3):
+        td.model.load_state_dict(st[0])
+        td.opt.load_state_dict(copy.deepcopy(st[1]))
+        ls.append(td.step(img, lab).item())
+    assert len(set(ls)) == 3
+    from vit_spectre_experiments_b200 import _lib
+    _lib.graph_seed["tensor"] = None

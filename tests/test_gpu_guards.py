@@ -133,13 +133,13 @@ def test_embed_guards(cuda_device):
     cls, pos = torch.randn(E, device=cuda_device), torch.randn(n + 1, E, device=cuda_device)
     out = g.alloc((B, n + 1, E), torch.bfloat16)
     _lib.check(lib.spectre_embed_finish_fwd(tok.data_ptr(), cls.data_ptr(), pos.data_ptr(), out.data_ptr(), B, n + 1, E, 1, 0.1, 3,
-                                            _st(cuda_device)), "finish_fwd")
+                                            None, _st(cuda_device)), "finish_fwd")
     dout = torch.randn(B, n + 1, E, device=cuda_device).bfloat16()
     dtok, dpos = g.alloc((B * n, E), torch.bfloat16), g.alloc((n + 1, E), torch.float32)
     nws = lib.spectre_embed_finish_bwd_workspace_bytes(B, n + 1, E)
     ws = g.alloc((max(nws, 16),), torch.uint8)
     _lib.check(lib.spectre_embed_finish_bwd(dout.data_ptr(), dtok.data_ptr(), dpos.data_ptr(), ws.data_ptr(), nws, B, n + 1, E, 1,
-                                            0.1, 3, _st(cuda_device)), "finish_bwd")
+                                            0.1, 3, None, _st(cuda_device)), "finish_bwd")
     g.check()
     ref = img.reshape(B, C, 8, P, 8, P).permute(0, 2, 4, 1, 3, 5).reshape(B * n, C * P * P).bfloat16()
     assert torch.equal(A, ref)

@@ -53,6 +53,7 @@ class NormActDesc(ctypes.Structure):
         ("act_dtype", ctypes.c_int), ("act", ctypes.c_int), ("eps", ctypes.c_float), ("drop_p", ctypes.c_float),
         ("seed", ctypes.c_ulonglong), ("reverse", ctypes.c_int),
         ("out_pool", ctypes.c_void_p), ("d_out_pool", ctypes.c_void_p), ("pool_k", ctypes.c_int),
+        ("seed_dev", ctypes.c_void_p),
     ]
 
 
@@ -107,9 +108,9 @@ def load() -> ctypes.CDLL:
         lib.spectre_norm_act_supported.restype = _i
         lib.spectre_patch_gather.argtypes = [_p, _p, _i, _i, _i, _i, _i, _i, _p]
         lib.spectre_patch_gather.restype = _i
-        lib.spectre_embed_finish_fwd.argtypes = [_p, _p, _p, _p, _i, _i, _i, _i, ctypes.c_float, ctypes.c_ulonglong, _p]
+        lib.spectre_embed_finish_fwd.argtypes = [_p, _p, _p, _p, _i, _i, _i, _i, ctypes.c_float, ctypes.c_ulonglong, _p, _p]
         lib.spectre_embed_finish_fwd.restype = _i
-        lib.spectre_embed_finish_bwd.argtypes = [_p, _p, _p, _p, _sz, _i, _i, _i, _i, ctypes.c_float, ctypes.c_ulonglong, _p]
+        lib.spectre_embed_finish_bwd.argtypes = [_p, _p, _p, _p, _sz, _i, _i, _i, _i, ctypes.c_float, ctypes.c_ulonglong, _p, _p]
         lib.spectre_embed_finish_bwd.restype = _i
         lib.spectre_embed_finish_bwd_workspace_bytes.argtypes = [_i, _i, _i]
         lib.spectre_embed_finish_bwd_workspace_bytes.restype = _sz
@@ -141,3 +142,14 @@ launch_counter = {"kernels": 0}
 
 def count_launches() -> None:
     launch_counter["kernels"] += load().spectre_last_launch_count()
+
+
+# Device word the dropout kernels add to their seeds (``seed_dev`` of include/spectre_b200.h).  A training step captured
+# in a CUDA graph freezes every host-side seed; train.Trainer(cuda_graph=True) installs an int64 device tensor here and
+# bumps it inside the graph, so each replay draws fresh masks (forward and backward of a replay read the same value).
+graph_seed = {"tensor": None}
+
+
+def seed_dev_ptr():
+    t = graph_seed["tensor"]
+    return None if t is None else t.data_ptr()

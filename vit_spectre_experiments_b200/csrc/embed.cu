@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(256) embed_finish_fwd_kernel(const T* __restri
     for (int e = 0; e < 8; ++e) base[e] += c[e];
   }
   const bool drop = a.drop_p > 0.f;
+  const na::Seed sd = drop ? na::load_seed(a) : na::Seed{0u, 0u};
   for (int b = blockIdx.y; b < B; b += gridDim.y) {
     float o[8];
     if (t == 0) {
@@ -97,7 +98,7 @@ __global__ void __launch_bounds__(256) embed_finish_fwd_kernel(const T* __restri
       for (int e = 0; e < 8; ++e) o[e] += base[e];
     }
     if (drop) {
-      const unsigned dm = na::drop_mask8(a, na::row_seed(a, static_cast<long long>(b) * Tn + t), static_cast<unsigned>(v));
+      const unsigned dm = na::drop_mask8(a, na::row_seed(sd, static_cast<long long>(b) * Tn + t), static_cast<unsigned>(v));
 #pragma unroll
       for (int e = 0; e < 8; ++e) o[e] = (dm >> e & 1u) ? 0.f : o[e] * a.keep_scale;
     }
@@ -113,6 +114,7 @@ __global__ void __launch_bounds__(256) embed_finish_bwd_kernel(const T* __restri
   if (idx >= Tn * nv) return;
   const int t = idx / nv, v = idx % nv;
   const bool drop = a.drop_p > 0.f;
+  const na::Seed sd = drop ? na::load_seed(a) : na::Seed{0u, 0u};
   float acc[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
@@ -120,7 +122,7 @@ __global__ void __launch_bounds__(256) embed_finish_bwd_kernel(const T* __restri
     float d[8];
     ld8<T>(dout + (static_cast<size_t>(b) * Tn + t) * E + v * 8, d);
     if (drop) {
-      const unsigned dm = na::drop_mask8(a, na::row_seed(a, static_cast<long long>(b) * Tn + t), static_cast<unsigned>(v));
+      const unsigned dm = na::drop_mask8(a, na::row_seed(sd, static_cast<long long>(b) * Tn + t), static_cast<unsigned>(v));
 #pragma unroll
       for (int e = 0; e < 8; ++e) d[e] = (dm >> e & 1u) ? 0.f : d[e] * a.keep_scale;
     }
@@ -176,7 +178,8 @@ static int embed_check(const char* fn, int B, int T, int E, int act_dtype, float
 }
 
 int spectre_embed_finish_fwd(const void* tok, const float* cls, const float* pos, void* out, int B, int T, int E,
-                             int act_dtype, float drop_p, unsigned long long seed, void* stream) {
+                             int act_dtype, float drop_p, unsigned long long seed, const unsigned long long* seed_dev,
+                             void* stream) {
   if (!tok || !cls || !pos || !out) return fail(SPECTRE_E_NULL, "spectre_embed_finish_fwd: null pointer");
   if (int rc = embed_check("spectre_embed_finish_fwd", B, T, E, act_dtype, drop_p)) return rc;
   if (!aligned16(tok) || !aligned16(cls) || !aligned16(pos) || !aligned16(out))
@@ -184,6 +187,7 @@ int spectre_embed_finish_fwd(const void* tok, const float* cls, const float* pos
   na::Args a{};
   na::set_dropout(a, drop_p);
   a.seed_lo = static_cast<unsigned>(seed); a.seed_hi = static_cast<unsigned>(seed >> 32);
+  a.seed_dev = seed_dev;
   const dim3 grid((T * (E / 8) + 255) / 256, embed::slabs_for(B, T, E));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (act_dtype == SPECTRE_DTYPE_BF16)
@@ -204,7 +208,8 @@ size_t spectre_embed_finish_bwd_workspace_bytes(int B, int T, int E) {
 }
 
 int spectre_embed_finish_bwd(const void* dout, void* dtok, float* dpos, void* workspace, size_t workspace_bytes, int B,
-                             int T, int E, int act_dtype, float drop_p, unsigned long long seed, void* stream) {
+                             int T, int E, int act_dtype, float drop_p, unsigned long long seed,
+                             const unsigned long long* seed_dev, void* stream) {
   if (!dout || !dtok || !dpos || !workspace) return fail(SPECTRE_E_NULL, "spectre_embed_finish_bwd: null pointer");
   if (int rc = embed_check("spectre_embed_finish_bwd", B, T, E, act_dtype, drop_p)) return rc;
   if (!aligned16(dout) || !aligned16(dtok) || !aligned16(dpos) || !aligned16(workspace))
@@ -215,6 +220,7 @@ int spectre_embed_finish_bwd(const void* dout, void* dtok, float* dpos, void* wo
   na::Args a{};
   na::set_dropout(a, drop_p);
   a.seed_lo = static_cast<unsigned>(seed); a.seed_hi = static_cast<unsigned>(seed >> 32);
+  a.seed_dev = seed_dev;
   const dim3 grid((T * (E / 8) + 255) / 256, slabs);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* part = static_cast<float*>(workspace);

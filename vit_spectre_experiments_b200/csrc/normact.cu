@@ -254,6 +254,7 @@ __global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(con
   const int nvec = a.N >> 3, S = a.stages;
   const float inv_n = 1.0f / static_cast<float>(a.N);
   const bool drop = a.drop_p > 0.f;
+  const Seed sd = drop ? load_seed(a) : Seed{0u, 0u};
   const float keep_scale = a.keep_scale;
   constexpr bool kFastGelu = std::is_same<T, __nv_bfloat16>::value;   // bf16 stream: tanh-form Phi (normact_common.cuh)
   const long long groups = (a.rows + a.rpc - 1) / a.rpc;
@@ -338,7 +339,7 @@ __global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(con
       }
       const float shift = -mean * rstd;
       const T* srow = reinterpret_cast<const T*>(st + off_skip) + rg * a.Ns;
-      const unsigned rseed = drop ? row_seed(a, row) : 0u;
+      const unsigned rseed = drop ? row_seed(sd, row) : 0u;
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
         const int v = t + i * tpr;
@@ -401,6 +402,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
   float* dn = reinterpret_cast<float*>(cov + a.Ns) + rg * a.N;
   const float inv_n = 1.0f / static_cast<float>(a.N);
   const bool drop = a.drop_p > 0.f;
+  const Seed sd = drop ? load_seed(a) : Seed{0u, 0u};
   const float keep_scale = a.keep_scale;
   constexpr bool kFastGelu = std::is_same<T, __nv_bfloat16>::value;   // bf16 stream: tanh-form Phi (normact_common.cuh)
   const long long groups = (a.rows + a.rpc - 1) / a.rpc;
@@ -465,7 +467,7 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
     ptx::mbar_wait(&full[stg], phase);
     const uint8_t* st = ring + stg * a.stage_bytes;
     const float shift = -mean * rstd;
-    const unsigned rseed = drop ? row_seed(a, row) : 0u;
+    const unsigned rseed = drop ? row_seed(sd, row) : 0u;
     float xh[VPT][8], gy[VPT][8];
     float s[2] = {0.f, 0.f};
 #pragma unroll
@@ -711,6 +713,7 @@ static Args to_args(const spectre_norm_act_t& d, bool bwd) {
   a.rows = d.rows; a.N = d.N; a.Ns = has_skip ? d.Ns : d.N; a.act = d.act; a.eps = d.eps;
   set_dropout(a, d.drop_p);
   a.seed_lo = static_cast<unsigned>(d.seed); a.seed_hi = static_cast<unsigned>(d.seed >> 32);
+  a.seed_dev = d.seed_dev;
   a.skip_mode = pick_skip(a.N, a.Ns, has_skip);
   a.reverse = d.reverse ? 1 : 0;
   return a;

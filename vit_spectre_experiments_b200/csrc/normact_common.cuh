@@ -30,6 +30,7 @@ struct Args {
   int tpr; int rpc;                                                 // threads per row, rows per CTA
   int stages; int stage_bytes;                                      // shared-memory ring of input row groups
   float eps; float drop_p; unsigned seed_lo; unsigned seed_hi;
+  const unsigned long long* seed_dev;   // optional device word added to the seed (CUDA-graph replays: the host seed is frozen)
   int reverse;   // sweep the row groups from the last to the first (the caller knows where the producer left L2 hot)
   // counter-based dropout (drop_mask8): thresholds derived from drop_p on the host
   unsigned drop_thresh;       // p * 2^32: an element is dropped iff its 32-bit draw is below this
@@ -171,13 +172,22 @@ __device__ __forceinline__ unsigned drop_mask8(const Args& a, unsigned rseed, un
   if (x >= a.drop_q32) return 0u;
   return drop_mask8_slow(a, x);
 }
+// call seed (+ the optional device-resident word: a captured graph bumps it between replays), read once per thread
+struct Seed {
+  unsigned lo, hi;
+};
+__device__ __forceinline__ Seed load_seed(const Args& a) {
+  unsigned long long s = static_cast<unsigned long long>(a.seed_hi) << 32 | a.seed_lo;
+  if (a.seed_dev) s += __ldg(a.seed_dev) * 0x9E3779B97F4A7C15ull;
+  return {static_cast<unsigned>(s), static_cast<unsigned>(s >> 32)};
+}
 // seed of a row (one 32-bit mix of the row index under the 64-bit call seed; drop_mask8 mixes the vector index in)
-__device__ __forceinline__ unsigned row_seed(const Args& a, long long row) {
-  unsigned x = static_cast<unsigned>(row) * 0x9E3779B1u + a.seed_lo;
+__device__ __forceinline__ unsigned row_seed(const Seed& sd, long long row) {
+  unsigned x = static_cast<unsigned>(row) * 0x9E3779B1u + sd.lo;
   x ^= x >> 16;
   x *= 0x7feb352du;
   x ^= x >> 15;
-  return x + (a.seed_hi ^ static_cast<unsigned>(row >> 32)) * 0x846ca68bu;
+  return x + (sd.hi ^ static_cast<unsigned>(row >> 32)) * 0x846ca68bu;
 }
 
 // ------------------------------------------------------------------ fast path (normact_fast.cu)

@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
     ptx::mbar_fence_init();
   }
   pdl_wait();   // nothing above touches global memory
+  const Seed sd = drop ? load_seed(a) : Seed{0u, 0u};
   if (threadIdx.x == 0)
     for (int it = 0; it < S - 1 && it < n_it; ++it) issue(it, it);
   for (int i = threadIdx.x; i < N; i += NT) {
@@ -96,7 +97,7 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
     }
     ptx::mbar_wait(&full[stg], phase);
     const u64 rs2 = splat(rstd), sh2 = splat(-mean * rstd);
-    const unsigned rseed = drop ? row_seed(a, row) : 0u;
+    const unsigned rseed = drop ? row_seed(sd, row) : 0u;
     __nv_bfloat16* dsrow = static_cast<__nv_bfloat16*>(a.d_skip) + row * NS;
     u64 xh[VPT][4], gy[VPT][4];
     u64 s0 = 0ull, s1 = 0ull;

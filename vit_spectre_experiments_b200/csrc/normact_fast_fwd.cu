@@ -57,6 +57,7 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
     ptx::mbar_fence_init();
   }
   pdl_wait();   // nothing above touches global memory
+  const Seed sd = drop ? load_seed(a) : Seed{0u, 0u};
   if (threadIdx.x == 0)
     for (int it = 0; it < S - 1 && it < n_it; ++it) issue(it, it);
   __syncthreads();
@@ -124,7 +125,7 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
       a.rstd[row] = rstd;
     }
     const u64 rs2 = splat(rstd), sh2 = splat(-dmean * rstd);
-    const unsigned rseed = drop ? row_seed(a, row) : 0u;
+    const unsigned rseed = drop ? row_seed(sd, row) : 0u;
     __nv_bfloat16* orow = static_cast<__nv_bfloat16*>(a.out) + row * N;
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {

@@ -257,7 +257,7 @@ class _PatchEmbed(torch.autograd.Function):
             clsf, posf = cls.detach().float().contiguous().view(-1), pos.detach().float().contiguous().view(n + 1, E)
             with _timed("embed_finish_fwd", (B * (n + 1), E, out.element_size(), (tok.numel() + out.numel()) * out.element_size())):
                 rc = lib.spectre_embed_finish_fwd(tok.data_ptr(), clsf.data_ptr(), posf.data_ptr(), out.data_ptr(), B, n + 1, E,
-                                                  code, float(drop_p), int(seed), st)
+                                                  code, float(drop_p), int(seed), _lib.seed_dev_ptr() if drop_p > 0 else None, st)
             _lib.check(rc, "spectre_embed_finish_fwd")
             _lib.count_launches()
         ctx.save_for_backward(A, Md)
@@ -277,7 +277,8 @@ class _PatchEmbed(torch.autograd.Function):
             ws = torch.empty(max(nws, 16), dtype=torch.uint8, device=A.device)
             with _timed("embed_finish_bwd", (B * (n + 1), E, dout.element_size(), (dout.numel() + dtok.numel()) * dout.element_size())):
                 rc = lib.spectre_embed_finish_bwd(dout.data_ptr(), dtok.data_ptr(), dpos.data_ptr(), ws.data_ptr(), nws, B, n + 1, E,
-                                                  code, drop_p, seed, _stream_ptr(A.device))
+                                                  code, drop_p, seed, _lib.seed_dev_ptr() if drop_p > 0 else None,
+                                                  _stream_ptr(A.device))
             _lib.check(rc, "spectre_embed_finish_bwd")
             _lib.count_launches()
         dM = torch.mm(A.t(), dtok).to(m_dt)

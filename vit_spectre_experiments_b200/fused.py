@@ -57,6 +57,7 @@ def na_fwd(in0, gamma, beta, in1=None, skip=None, eps=1e-5, act=0, drop_p=0.0, s
     d.rows, d.N, d.Ns = rows, N, (skip.shape[-1] if skip is not None else N)
     d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
     d.reverse = int(bool(reverse))
+    d.seed_dev = _lib.seed_dev_ptr() if drop_p > 0 else None
     out_pool = None
     if pool_k:
         out_pool = torch.empty(rows, N // pool_k, dtype=in0.dtype, device=in0.device)
@@ -94,6 +95,7 @@ def na_bwd(dout, in0, gamma, beta, mean, rstd, in1=None, skip_shape=None, eps=1e
     d.rows, d.N, d.Ns = rows, N, (skip_shape[-1] if skip_shape is not None else N)
     d.act_dtype, d.act, d.eps, d.drop_p, d.seed = _DT[in0.dtype], int(act), float(eps), float(drop_p), int(seed)
     d.reverse = int(bool(reverse))
+    d.seed_dev = _lib.seed_dev_ptr() if drop_p > 0 else None
     if d_out_pool is not None:
         d.d_out_pool, d.pool_k = _ptr(d_out_pool), int(pool_k)
     nbytes = (in0.numel() * (3 + (in1 is not None) + (dout2 is not None)) + (d_skip.numel() if d_skip is not None else 0)

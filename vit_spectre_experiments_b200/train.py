@@ -87,7 +87,8 @@ class Trainer:
     (DDP all-reduce overlapped) -> fused AdamW.  ``step`` returns the loss tensor without syncing."""
 
     def __init__(self, cfg: SimpleNamespace, device, *, mixer: str | None = None, model: nn.Module | None = None,
-                 ddp: bool | None = None, seed: int | None = None, teacher: nn.Module | None = None):
+                 ddp: bool | None = None, seed: int | None = None, teacher: nn.Module | None = None,
+                 cuda_graph: bool = False):
         self.cfg, self.device = cfg, torch.device(device)
         torch.manual_seed(cfg.random_seed if seed is None else seed)
         self.model = (model if model is not None else build_model(cfg, mixer)).to(self.device)
@@ -106,12 +107,19 @@ class Trainer:
         world = dist.get_world_size() if dist.is_initialized() else 1
         self.world = world
         self.net = self.model
-        if (ddp if ddp is not None else world > 1) and world > 1:
+        # cuda_graph: the whole step (forward, loss, backward, gradient all-reduce, AdamW) is captured once and
+        # replayed -- the C ABI only enqueues work on the current stream, so it is capturable as it stands.  The small
+        # configs (C1-C3: ~180 launches in a few ms) are launch-bound in eager mode.  Gradients are all-reduced as one
+        # flat NCCL call inside the graph instead of DDP buckets.
+        self.cuda_graph = bool(cuda_graph) and self.device.type == "cuda"
+        self._graph = None
+        if (ddp if ddp is not None else world > 1) and world > 1 and not self.cuda_graph:
             ids = [self.device.index] if self.device.type == "cuda" else None
             self.net = nn.parallel.DistributedDataParallel(self.model, device_ids=ids, gradient_as_bucket_view=True,
                                                            static_graph=True)
         self.opt = torch.optim.AdamW(self.model.parameters(), lr=cfg.learning_rate, betas=cfg.adam_betas,
-                                     weight_decay=cfg.adam_weight_decay, fused=self.device.type == "cuda")
+                                     weight_decay=cfg.adam_weight_decay, fused=self.device.type == "cuda",
+                                     capturable=self.cuda_graph)
 
     def synthetic_batch(self, batch: int, rank: int = 0, pinned_host: bool = False):
         """Synthetic data of the configured shape: ``randn`` images, uniform labels, seed 42 + rank."""
@@ -135,13 +143,59 @@ class Trainer:
         c = self.cfg
         return kd_loss(logits, t_logits, lab, c.distill_temperature, c.distill_soft_weight, c.distill_ce_weight)
 
-    def step(self, img, lab):
-        self.net.train()
+    def _allreduce_grads(self):
+        """One flat all-reduce (mean) of every gradient: the graph-mode stand-in for DDP's buckets."""
+        grads = [p.grad for p in self.model.parameters() if p.grad is not None]
+        flat = torch.cat([g.reshape(-1).float() for g in grads])
+        dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+        torch._foreach_copy_(grads, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in grads]), grads)])
+
+    def _eager_step(self, img, lab):
         loss = self.forward_loss(img, lab)
         self.opt.zero_grad(set_to_none=True)
         loss.backward()
+        if self.cuda_graph and self.world > 1:
+            self._allreduce_grads()
         self.opt.step()
         return loss.detach()
+
+    def _capture(self, img, lab):
+        from . import _lib
+
+        self._g_img, self._g_lab = torch.empty_like(img), torch.empty_like(lab)
+        self._g_img.copy_(img)
+        self._g_lab.copy_(lab)
+        self._seed_word = torch.zeros(1, dtype=torch.int64, device=self.device)
+        _lib.graph_seed["tensor"] = self._seed_word            # dropout seeds: host part frozen, this word bumped per replay
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):                          # warm-up off the capture: lazy inits, allocator, autotune
+            for _ in range(3):
+                self._seed_word += 1
+                self._eager_step(self._g_img, self._g_lab)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        before = _lib.launch_counter["kernels"]
+        self._graph = torch.cuda.CUDAGraph()
+        self.opt.zero_grad(set_to_none=True)
+        with torch.cuda.graph(self._graph):
+            self._seed_word += 1
+            self._g_loss = self._eager_step(self._g_img, self._g_lab)
+        self._launches_per_replay = _lib.launch_counter["kernels"] - before
+
+    def step(self, img, lab):
+        self.net.train()
+        if not self.cuda_graph:
+            return self._eager_step(img, lab)
+        from . import _lib
+
+        if self._graph is None:
+            self._capture(img, lab)
+        if img.data_ptr() != self._g_img.data_ptr():
+            self._g_img.copy_(img, non_blocking=True)
+            self._g_lab.copy_(lab, non_blocking=True)
+        self._graph.replay()
+        _lib.launch_counter["kernels"] += self._launches_per_replay
+        return self._g_loss
 
 
 class HostBatchPrefetcher:
