@@ -418,7 +418,6 @@ def test_training_step_is_cuda_graph_capturable(cuda_device, mixer, precision):
     (forward, loss, backward with the fused parameter-gradient reductions, AdamW) is captured in one CUDA graph by
     ``Trainer(cuda_graph=True)`` and replayed.  A replay from the same state is bit-identical; against the eager step
     it agrees to rounding; with dropout on, every replay draws a fresh mask through the device-resident seed word."""
-    import copy
     from types import SimpleNamespace
 
     from vit_spectre_experiments_b200.train import Trainer
@@ -428,14 +427,26 @@ def test_training_step_is_cuda_graph_capturable(cuda_device, mixer, precision):
                                num_heads=4, hidden_dim=256, dropout=p, activation="gelu", mixer=mixer, precision=precision,
                                random_seed=42, learning_rate=1e-3, adam_betas=(0.9, 0.999), adam_weight_decay=0.01)
 
+    def snapshot(tr):
+        """Parameters and AdamW state, to be restored IN PLACE (the captured graph holds the tensors' addresses)."""
+        return ([p.detach().clone() for p in tr.model.parameters()],
+                [{k: v.clone() for k, v in tr.opt.state[p].items() if torch.is_tensor(v)} for p in tr.model.parameters()])
+
+    def restore(tr, snap):
+        with torch.no_grad():
+            for p, q in zip(tr.model.parameters(), snap[0]):
+                p.copy_(q)
+            for p, st in zip(tr.model.parameters(), snap[1]):
+                for k, v in st.items():
+                    tr.opt.state[p][k].copy_(v)
+
     tg = Trainer(cfg(0.0), cuda_device, cuda_graph=True)
     img, lab = tg.synthetic_batch(32)
     tg.step(img, lab)                                   # 3 eager warm-up steps + capture + first replay
-    state = (copy.deepcopy(tg.model.state_dict()), copy.deepcopy(tg.opt.state_dict()))
+    state = snapshot(tg)
 
     def replay_from_state():
-        tg.model.load_state_dict(state[0])
-        tg.opt.load_state_dict(copy.deepcopy(state[1]))
+        restore(tg, state)
         loss = tg.step(img, lab).clone()
         return loss, [p.detach().clone() for p in tg.model.parameters()]
 
@@ -443,8 +454,7 @@ def test_training_step_is_cuda_graph_capturable(cuda_device, mixer, precision):
     lb, pb = replay_from_state()
     assert torch.equal(la, lb) and all(torch.equal(u, v) for u, v in zip(pa, pb))
     # the same step, eagerly, from the same state
-    tg.model.load_state_dict(state[0])
-    tg.opt.load_state_dict(copy.deepcopy(state[1]))
+    restore(tg, state)
     le = tg._eager_step(img, lab)
     assert abs(le.item() - la.item()) <= 1e-5 * abs(la.item()) + 1e-6
     for u, v in zip(pa, tg.model.parameters()):
@@ -454,11 +464,10 @@ def test_training_step_is_cuda_graph_capturable(cuda_device, mixer, precision):
     # dropout inside a graph: fresh masks per replay
     td = Trainer(cfg(0.3), cuda_device, cuda_graph=True)
     td.step(img, lab)
-    st = (copy.deepcopy(td.model.state_dict()), copy.deepcopy(td.opt.state_dict()))
+    st = snapshot(td)
     ls = []
     for _ in range(3):
-        td.model.load_state_dict(st[0])
-        td.opt.load_state_dict(copy.deepcopy(st[1]))
+        restore(td, st)
         ls.append(td.step(img, lab).item())
     assert len(set(ls)) == 3
     from vit_spectre_experiments_b200 import _lib
