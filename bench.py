@@ -10,11 +10,13 @@ GPU.  Default workload: BASELINE.json configs[3] (ViT-S/16 FFT-mix, 224^2 -> 14x
 configs/vit_s16_fft.py:bench_batch_size; --batch 256 gives SURVEY.md's batch) -- the configuration the north-star's
 scaling target is quoted on.
 
-  value     images/s, inputs resident in HBM, CUDA events, max over ranks
+  value     images/s, inputs resident in HBM, CUDA events, max over ranks.  The step is captured once in a CUDA graph
+            (train.Trainer(cuda_graph=True)) and the timed region replays it; --no-cuda-graph times eager steps
   e2e       same through the public API with HOST buffers: every step copies the batch from pinned host
             memory and reads the loss back
-  roofline  dominant mixer kernel (the fused backward), timed live with CUDA events inside the timed
-            steps; algorithmic bytes = 3*B*T*E*s + 2*F / mean launch time
+  roofline  dominant mixer kernel (the fused backward), timed with CUDA events on the launching stream: inside the
+            timed steps with --no-cuda-graph; by default (events cannot be recorded inside a replayed graph) in an
+            eager pass of the same steps right after the timed replays; algorithmic bytes = 3*B*T*E*s + 2*F / mean launch time
   cpu_baseline  the oracle port of the reference's PyTorch path (reference model classes' mirror with the
             torch.fft / Haar composition in the mix_layer slot) on the host cores, bounded sample
 --impl reference runs only that CPU arm (rank 0; other ranks exit 0).
@@ -181,8 +183,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cuda-graph", action="store_true",
-                    help="capture the whole step (fwd, bwd, gradient all-reduce, AdamW) in one CUDA graph and replay it")
+    ap.add_argument("--no-cuda-graph", dest="cuda_graph", action="store_false",
+                    help="eager steps with DDP buckets instead of the default: the whole step (fwd, bwd, gradient "
+                         "all-reduce, AdamW) captured in one CUDA graph and replayed")
     args = ap.parse_args()
 
     from vit_spectre_experiments_b200.configs import load_named
