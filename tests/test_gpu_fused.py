@@ -35,6 +35,11 @@ CASES = [
     ((6, 197), 384, None, torch.float32, True, "none"),
     ((3, 65), 768, 512, torch.float32, False, "gelu"),      # C1 widths: general adaptive pool 512 -> 768
     ((3, 65), 512, 768, torch.float32, False, "gelu"),      #            and 768 -> 512
+    ((3, 65), 768, 512, torch.bfloat16, False, "gelu"),     # C3 (bf16 stream): the fast kernels' 3:2 modes
+    ((3, 65), 512, 768, torch.bfloat16, False, "gelu"),
+    ((41, 7), 768, 512, torch.bfloat16, False, "none"),     # 3:2 up without activation (forward fast, backward generic)
+    ((41, 7), 1536, 1024, torch.bfloat16, False, "gelu"),   # other widths in ratio 3:2
+    ((41, 7), 1024, 1536, torch.bfloat16, True, "gelu"),
     ((5, 50), 48, 48, torch.float32, False, "none"),        # C2 width 48 (single partial warp)
     ((5, 50), 256, 48, torch.float32, False, "gelu"),       # 48 -> 256 (general)
     ((5, 50), 48, 256, torch.float32, False, "gelu"),       # 256 -> 48 (general)

@@ -111,6 +111,57 @@ __device__ __forceinline__ void row_sum2(float& a, float& b, float (*red)[2][RW]
   }
 }
 
+// Skip modes that only the fast kernels know (the generic kernels treat these ratios as table-driven "general" pooling):
+// AdaptiveAvgPool1d between widths in ratio 3:2, the 512 <-> 768 of the reference's CIFAR configs
+// (configs/spectre_vit_cifar100.py:17-19).  Up (N = 3/2 Ns):  out[3k] = s[2k], out[3k+1] = (s[2k] + s[2k+1]) / 2,
+// out[3k+2] = s[2k+1];  down (N = 2/3 Ns):  out[2k] = (s[3k] + s[3k+1]) / 2, out[2k+1] = (s[3k+1] + s[3k+2]) / 2.
+// The pattern has period 3 resp. 2 in the output, so a thread owns VPT CONSECUTIVE vectors (24 resp. 16 columns facing
+// 16 resp. 24 skip columns) and every index below is a compile-time constant.
+enum : int { kFastUp32 = 100, kFastDown32 = 101 };
+constexpr bool contig_mode(int mode) { return mode == kFastUp32 || mode == kFastDown32; }
+constexpr int skip_width(int mode, int N) {
+  return mode == kSkipIdentity ? N : mode == kSkipUp4 ? N / 4 : mode == kFastUp32 ? N / 3 * 2 : mode == kFastDown32 ? N / 2 * 3 : 0;
+}
+// vector owned by thread t as its i-th: strided by the threads of the row, or consecutive for the 3:2 modes
+template <int MODE, int VPT, int TPR>
+__device__ __forceinline__ int vec_of(int t, int i) { return contig_mode(MODE) ? t * VPT + i : t + i * TPR; }
+// pooled skip value facing local output column jl (0 .. 8 VPT) of a thread, from its local skip columns sk[]
+template <int MODE>
+__device__ __forceinline__ float skip32_val(const float* sk, int jl) {
+  if constexpr (MODE == kFastUp32) {
+    const int k = jl / 3, m = jl % 3;
+    return m == 0 ? sk[2 * k] : m == 2 ? sk[2 * k + 1] : 0.5f * (sk[2 * k] + sk[2 * k + 1]);
+  } else {
+    const int k = jl / 2, m = jl % 2;
+    return 0.5f * (sk[3 * k + m] + sk[3 * k + m + 1]);
+  }
+}
+// transpose: scatter the gradient d of local output column jl into the local skip-gradient accumulators ds[]
+template <int MODE>
+__device__ __forceinline__ void skip32_scatter(float* ds, int jl, float d) {
+  if constexpr (MODE == kFastUp32) {
+    const int k = jl / 3, m = jl % 3;
+    if (m == 0) ds[2 * k] += d;
+    else if (m == 2) ds[2 * k + 1] += d;
+    else { ds[2 * k] = fmaf(0.5f, d, ds[2 * k]); ds[2 * k + 1] = fmaf(0.5f, d, ds[2 * k + 1]); }
+  } else {
+    const int k = jl / 2, m = jl % 2;
+    ds[3 * k + m] = fmaf(0.5f, d, ds[3 * k + m]);
+    ds[3 * k + m + 1] = fmaf(0.5f, d, ds[3 * k + m + 1]);
+  }
+}
+__device__ __forceinline__ void unpack8(uint4 q, float* v) {
+  v[0] = bf_lo(q.x); v[1] = bf_hi(q.x); v[2] = bf_lo(q.y); v[3] = bf_hi(q.y);
+  v[4] = bf_lo(q.z); v[5] = bf_hi(q.z); v[6] = bf_lo(q.w); v[7] = bf_hi(q.w);
+}
+// fast mode of a launch: the generic skip mode, or one of the 3:2 modes when the widths say so; -1: not covered
+inline int fast_mode(int skip_mode, int N, int Ns) {
+  if (skip_mode == kSkipNone || skip_mode == kSkipIdentity || skip_mode == kSkipUp4) return skip_mode;
+  if (skip_mode == kSkipGeneral && 2 * N == 3 * Ns && N % 24 == 0) return kFastUp32;
+  if (skip_mode == kSkipGeneral && 3 * N == 2 * Ns && N % 16 == 0) return kFastDown32;
+  return -1;
+}
+
 // Shape of a fast launch: N = 8 * VPT * TPR exactly (no idle lanes, no column predicates)
 struct FastShape {
   int vpt, tpr;

@@ -20,8 +20,8 @@ namespace na {
 template <int VPT, int TPR, int RPC, int MODE, int ACT, int NACC>
 __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
   constexpr int N = 8 * VPT * TPR, NV = N / 8, NT = TPR * RPC;
-  constexpr int NS = MODE == kSkipIdentity ? N : MODE == kSkipUp4 ? N / 4 : 0;
-  static_assert(MODE == kSkipNone || MODE == kSkipIdentity || MODE == kSkipUp4, "fast backward skip modes");
+  constexpr int NS = skip_width(MODE, N);
+  static_assert(!contig_mode(MODE) || (MODE == kFastUp32 ? VPT == 3 : VPT == 2), "3:2 modes: 24 or 16 columns per thread");
   extern __shared__ __align__(128) uint8_t ring[];
   __shared__ uint64_t full[kMaxStages];
   __shared__ float red[2][2][16];
@@ -102,9 +102,14 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
     u64 xh[VPT][4], gy[VPT][4];
     u64 s0 = 0ull, s1 = 0ull;
     if (live) {   // rows past the end (last group only) hold stale shared memory: they must not reach the accumulators
+    float ds[contig_mode(MODE) ? NS / TPR : 1];   // 3:2 modes: gradient of this thread's 16 / 24 skip columns
+    if constexpr (contig_mode(MODE)) {
+#pragma unroll
+      for (int q = 0; q < NS / TPR; ++q) ds[q] = 0.f;
+    }
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
-      const int v = t + i * TPR, j0 = v * 8;
+      const int v = vec_of<MODE, VPT, TPR>(t, i), j0 = v * 8;
       const uint4 qd = (reinterpret_cast<const uint4*>(st) + rg * NV)[v];
       const uint4 qz = (reinterpret_cast<const uint4*>(st + kOp) + rg * NV)[v];
       const unsigned wd[4] = {qd.x, qd.y, qd.z, qd.w}, wz[4] = {qz.x, qz.y, qz.z, qz.w};
@@ -146,6 +151,14 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
         *reinterpret_cast<uint4*>(dsrow + j0) = make_uint4(bfpack2(d[0]), bfpack2(d[1]), bfpack2(d[2]), bfpack2(d[3]));
       } else if constexpr (MODE == kSkipUp4) {
         reinterpret_cast<unsigned*>(dsrow)[v] = bf_pack(hsum(add2(d[0], d[1])), hsum(add2(d[2], d[3])));
+      } else if constexpr (contig_mode(MODE)) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float lo, hi;
+          upk(d[k], lo, hi);
+          skip32_scatter<MODE>(ds, 8 * i + 2 * k, lo);
+          skip32_scatter<MODE>(ds, 8 * i + 2 * k + 1, hi);
+        }
       }
       // ---- main path
       const float4 ga = *reinterpret_cast<const float4*>(sgb + j0), gb = *reinterpret_cast<const float4*>(sgb + j0 + 4);
@@ -176,6 +189,13 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
         s1 = fma2(y, x, s1);
       }
     }
+    if constexpr (contig_mode(MODE)) {
+      uint4* dp = reinterpret_cast<uint4*>(dsrow) + t * (NS / TPR / 8);
+#pragma unroll
+      for (int q = 0; q < NS / TPR / 8; ++q)
+        dp[q] = make_uint4(bf_pack(ds[8 * q], ds[8 * q + 1]), bf_pack(ds[8 * q + 2], ds[8 * q + 3]),
+                           bf_pack(ds[8 * q + 4], ds[8 * q + 5]), bf_pack(ds[8 * q + 6], ds[8 * q + 7]));
+    }
     }
     float sa = hsum(s0), sb = hsum(s1);
     row_sum2<TPR>(sa, sb, red, it & 1, rg);
@@ -190,7 +210,7 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
           dz[k] = fma2(xh[i][k], cx, fma2(gy[i][k], cr, cb));
           if constexpr (NACC == 3) acc[2][i][k] = add2(acc[2][i][k], dz[k]);
         }
-        *reinterpret_cast<uint4*>(drow + (t + i * TPR) * 8) =
+        *reinterpret_cast<uint4*>(drow + vec_of<MODE, VPT, TPR>(t, i) * 8) =
             make_uint4(bfpack2(dz[0]), bfpack2(dz[1]), bfpack2(dz[2]), bfpack2(dz[3]));
       }
     }
@@ -205,7 +225,7 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
   for (int n = 0; n < NACC; ++n) {
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
-      float* dst = fold + rg * N + (t + i * TPR) * 8;
+      float* dst = fold + rg * N + vec_of<MODE, VPT, TPR>(t, i) * 8;
       float v[8];
 #pragma unroll
       for (int k = 0; k < 4; ++k) upk(acc[n][i][k], v[2 * k], v[2 * k + 1]);
@@ -242,6 +262,8 @@ static FastFn pick_bwd(int mode, int nacc) {
   if (mode == kSkipNone) return pick_bwd_mode<VPT, TPR, RPC, kSkipNone, ACT>(nacc);
   if (mode == kSkipIdentity) return pick_bwd_mode<VPT, TPR, RPC, kSkipIdentity, ACT>(nacc);
   if (mode == kSkipUp4) return pick_bwd_mode<VPT, TPR, RPC, kSkipUp4, ACT>(nacc);
+  if constexpr (VPT == 3 && ACT == 1) { if (mode == kFastUp32) return pick_bwd_mode<VPT, TPR, RPC, kFastUp32, ACT>(nacc); }
+  if constexpr (VPT == 2 && ACT == 1) { if (mode == kFastDown32) return pick_bwd_mode<VPT, TPR, RPC, kFastDown32, ACT>(nacc); }
   return nullptr;
 }
 
@@ -250,8 +272,9 @@ int fast_bwd_grid_bound() { return device_sm_count(); }
 bool fast_bwd_launch(const Args& a0, size_t workspace_bytes, cudaStream_t st, int* rc, int* grid_out) {
   FastShape fs;
   if (!fast_shape(a0.N, true, &fs)) return false;
-  if (a0.skip_mode != kSkipNone && a0.skip_mode != kSkipIdentity && a0.skip_mode != kSkipUp4) return false;
-  if (a0.d_out_pool && a0.pool_k != 4) return false;
+  const int mode = fast_mode(a0.skip_mode, a0.N, a0.Ns);
+  if (mode < 0) return false;
+  if (a0.d_out_pool && (a0.pool_k != 4 || contig_mode(mode))) return false;
   FastFn fn = nullptr;
   int threads = 0;
   // rows per CTA: the GELU kernels are issue-bound at 8-12 warps per SM (profiles/r02_ncu_normact_fast_v1.txt), so
@@ -259,10 +282,10 @@ bool fast_bwd_launch(const Args& a0, size_t workspace_bytes, cudaStream_t st, in
 #define SB200_SHAPE(V, T, R0, R1)                                              \
   if (fs.vpt == V && fs.tpr == T) {                                            \
     if (a0.act) {                                                              \
-      fn = pick_bwd<V, T, R1, 1>(a0.skip_mode, a0.nacc);                          \
+      fn = pick_bwd<V, T, R1, 1>(mode, a0.nacc);                          \
       threads = T * R1;                                                        \
     } else {                                                                   \
-      fn = pick_bwd<V, T, R0, 0>(a0.skip_mode, a0.nacc);                          \
+      fn = pick_bwd<V, T, R0, 0>(mode, a0.nacc);                          \
       threads = T * R0;                                                        \
     }                                                                          \
   }

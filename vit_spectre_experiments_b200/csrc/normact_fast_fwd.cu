@@ -22,8 +22,8 @@ constexpr int fwd_threads(int tpr) { return 320 % tpr == 0 ? 320 : 256; }
 template <int VPT, int TPR, int MODE, int ACT>
 __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Args a) {
   constexpr int N = 8 * VPT * TPR, RPC = fwd_threads(TPR) / TPR, NV = N / 8;
-  constexpr int NS = MODE == kSkipIdentity ? N : MODE == kSkipUp4 ? N / 4 : 0;
-  static_assert(MODE == kSkipNone || MODE == kSkipIdentity || MODE == kSkipUp4, "fast forward skip modes");
+  constexpr int NS = skip_width(MODE, N);
+  static_assert(!contig_mode(MODE) || (MODE == kFastUp32 ? VPT == 3 : VPT == 2), "3:2 modes: 24 or 16 columns per thread");
   extern __shared__ __align__(128) uint8_t ring[];
   __shared__ uint64_t full[kMaxStages];
   __shared__ float red[2][2][16];
@@ -71,8 +71,8 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
   for (int i = 0; i < VPT; ++i)
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      gam[i][k] = ldg2(a.gamma + (t + i * TPR) * 8 + 2 * k);
-      bet[i][k] = ldg2(a.beta + (t + i * TPR) * 8 + 2 * k);
+      gam[i][k] = ldg2(a.gamma + vec_of<MODE, VPT, TPR>(t, i) * 8 + 2 * k);
+      bet[i][k] = ldg2(a.beta + vec_of<MODE, VPT, TPR>(t, i) * 8 + 2 * k);
     }
   constexpr float inv_n = 1.0f / N;
   int stg = 0;
@@ -93,12 +93,12 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
     u64 d[VPT][4], s0[VPT], s1[VPT];
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
-      const uint4 q = r0[t + i * TPR];
+      const uint4 q = r0[vec_of<MODE, VPT, TPR>(t, i)];
       const unsigned w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
       for (int k = 0; k < 4; ++k) d[i][k] = bf2_add(w[k], npiv);
       if (has_in1) {
-        const uint4 q1 = r1[t + i * TPR];
+        const uint4 q1 = r1[vec_of<MODE, VPT, TPR>(t, i)];
         const unsigned w1[4] = {q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
         for (int k = 0; k < 4; ++k) d[i][k] = bf2_add(w1[k], d[i][k]);
@@ -127,9 +127,15 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
     const u64 rs2 = splat(rstd), sh2 = splat(-dmean * rstd);
     const unsigned rseed = drop ? row_seed(sd, row) : 0u;
     __nv_bfloat16* orow = static_cast<__nv_bfloat16*>(a.out) + row * N;
+    float sk[contig_mode(MODE) ? NS / TPR : 1];   // 3:2 modes: this thread's 16 / 24 skip columns
+    if constexpr (contig_mode(MODE)) {
+      const uint4* sp = reinterpret_cast<const uint4*>(st + off_skip) + rg * (NS / 8) + t * (NS / TPR / 8);
+#pragma unroll
+      for (int q = 0; q < NS / TPR / 8; ++q) unpack8(sp[q], sk + 8 * q);
+    }
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
-      const int v = t + i * TPR, j0 = v * 8;
+      const int v = vec_of<MODE, VPT, TPR>(t, i), j0 = v * 8;
       u64 r[4];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
@@ -150,6 +156,10 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
         const unsigned w = (reinterpret_cast<const unsigned*>(st + off_skip) + rg * (NS / 2))[v];
         const u64 sl = splat(bf_lo(w)), sh = splat(bf_hi(w));
         r[0] = add2(r[0], sl); r[1] = add2(r[1], sl); r[2] = add2(r[2], sh); r[3] = add2(r[3], sh);
+      } else if constexpr (contig_mode(MODE)) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          r[k] = add2(r[k], pk(skip32_val<MODE>(sk, 8 * i + 2 * k), skip32_val<MODE>(sk, 8 * i + 2 * k + 1)));
       }
       if (drop) {
         const unsigned dm = drop_mask8(a, rseed, static_cast<unsigned>(v));
@@ -187,6 +197,8 @@ static FastFn pick_fwd(int mode, int act) {
   SB200_ROW(kSkipNone)
   SB200_ROW(kSkipIdentity)
   SB200_ROW(kSkipUp4)
+  if constexpr (VPT == 3) { SB200_ROW(kFastUp32) }
+  if constexpr (VPT == 2) { SB200_ROW(kFastDown32) }
 #undef SB200_ROW
   return nullptr;
 }
@@ -194,17 +206,18 @@ static FastFn pick_fwd(int mode, int act) {
 bool fast_fwd_launch(const Args& a0, cudaStream_t st, int* rc) {
   FastShape fs;
   if (!fast_shape(a0.N, false, &fs)) return false;
-  if (a0.skip_mode != kSkipNone && a0.skip_mode != kSkipIdentity && a0.skip_mode != kSkipUp4) return false;
-  if (a0.out_pool && a0.pool_k != 4) return false;
+  const int mode = fast_mode(a0.skip_mode, a0.N, a0.Ns);
+  if (mode < 0) return false;
+  if (a0.out_pool && (a0.pool_k != 4 || contig_mode(mode))) return false;
   FastFn fn = nullptr;
-#define SB200_SHAPE(V, T) if (fs.vpt == V && fs.tpr == T) fn = pick_fwd<V, T>(a0.skip_mode, a0.act ? 1 : 0);
+#define SB200_SHAPE(V, T) if (fs.vpt == V && fs.tpr == T) fn = pick_fwd<V, T>(mode, a0.act ? 1 : 0);
   SB200_SHAPE(3, 16) SB200_SHAPE(3, 32) SB200_SHAPE(3, 64) SB200_SHAPE(3, 128)
   SB200_SHAPE(2, 16) SB200_SHAPE(2, 32) SB200_SHAPE(2, 64) SB200_SHAPE(2, 128)
 #undef SB200_SHAPE
   if (!fn) return false;
   Args a = a0;
   const int threads = fwd_threads(fs.tpr), rpc = threads / fs.tpr;
-  const int ns = a.skip_mode == kSkipIdentity ? a.N : a.skip_mode == kSkipUp4 ? a.N / 4 : 0;
+  const int ns = skip_width(mode, a.N);
   const int row_bytes = a.N * 2 * (a.in1 ? 2 : 1) + ns * 2;
   a.tpr = fs.tpr; a.rpc = rpc;
   a.stage_bytes = (rpc * row_bytes + 127) / 128 * 128;
