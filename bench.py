@@ -388,6 +388,14 @@ def main():
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier(device_ids=[local_rank])
+        torch.cuda.synchronize()
+        if args.cuda_graph:
+            # a live CUDA graph that captured NCCL kernels keeps the communicator busy: tearing the process group down
+            # hung (observed: torchrun killed by its timeout after the JSON line).  Every rank is past the last
+            # collective here, so leave without the teardown.
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os._exit(0)
         dist.destroy_process_group()
 
 
