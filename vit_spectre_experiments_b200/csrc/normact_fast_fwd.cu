@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
   static_assert(!contig_mode(MODE) || (MODE == kFastUp32 ? VPT == 3 : VPT == 2), "3:2 modes: 24 or 16 columns per thread");
   extern __shared__ __align__(128) uint8_t ring[];
   __shared__ uint64_t full[kMaxStages];
-  __shared__ float red[2][2][16];
+  __shared__ float red[4][2][16];
   const int rg = threadIdx.x / TPR, t = threadIdx.x % TPR;
   const int S = a.stages;
   const bool has_in1 = a.in1 != nullptr;
@@ -58,8 +58,10 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
   }
   pdl_wait();   // nothing above touches global memory
   const Seed sd = drop ? load_seed(a) : Seed{0u, 0u};
+  // the ring is consumed in groups of kGroup row groups: one CTA-wide barrier and one refill round per group
+  constexpr int kGroup = 2;
   if (threadIdx.x == 0)
-    for (int it = 0; it < S - 1 && it < n_it; ++it) issue(it, it);
+    for (int it = 0; it < S - kGroup && it < n_it; ++it) issue(it, it);
   __syncthreads();
 
   const u64 c0 = splat(kGeluC0), c1 = splat(kGeluC1), c2 = splat(kGeluC2), half2 = splat(0.5f);
@@ -80,7 +82,11 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
   long long row = first0 + rg;
   const uint8_t* st = ring;
   for (int it = 0; it < n_it; ++it, row += gstep) {
-    if (threadIdx.x == 0 && it + S - 1 < n_it) issue(it + S - 1, stg == 0 ? S - 1 : stg - 1);   // the stage freed by it-1
+    if (threadIdx.x == 0 && it % kGroup == 0) {   // the stages of the previous group are free (barrier below)
+#pragma unroll 1
+      for (int k = 0; k < kGroup; ++k)
+        if (it + S - kGroup + k < n_it) issue(it + S - kGroup + k, (it + S - kGroup + k) % S);
+    }
     ptx::mbar_wait(&full[stg], phase);
     const bool live = row < a.rows;
     const uint4* r0 = reinterpret_cast<const uint4*>(st) + rg * NV;
@@ -116,7 +122,7 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
       s1[0] = add2(s1[0], s1[i]);
     }
     float sa = hsum(s0[0]), sb = hsum(s1[0]);
-    row_sum2<TPR>(sa, sb, red, it & 1, rg);
+    row_sum2<TPR>(sa, sb, red, it & 3, rg);
     const float dmean = sa * inv_n;
     const float var = fmaxf(fmaf(-dmean, dmean, sb * inv_n), 0.f);
     const float rstd = rsqrtf(var + a.eps);
@@ -182,7 +188,7 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
         }
       }
     }
-    __syncthreads();   // every thread is done with this stage: the producer may refill it
+    if (it % kGroup == kGroup - 1 || it + 1 == n_it) __syncthreads();   // the group is consumed: its stages may be refilled
     st += a.stage_bytes;
     if (++stg == S) { stg = 0; phase ^= 1u; st = ring; }
   }
@@ -224,7 +230,7 @@ bool fast_fwd_launch(const Args& a0, cudaStream_t st, int* rc) {
   // two CTAs per SM: ring of up to ~100 KB each
   int stages = (100 * 1024) / a.stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
-  if (stages < 2) return false;
+  if (stages < 3) return false;   // 2 stages being read + at least 1 in flight
   a.stages = stages;
   const size_t smem = static_cast<size_t>(stages) * a.stage_bytes;
   if (ensure_dynamic_smem(reinterpret_cast<const void*>(fn), kMaxSmem) != cudaSuccess) {
