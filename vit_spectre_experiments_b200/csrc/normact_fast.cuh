@@ -4,6 +4,8 @@
 // unpack instruction), sub-warp / multi-warp row sums.
 #pragma once
 
+#include <cstdlib>
+
 #include "normact_common.cuh"
 
 namespace sb200 {
@@ -174,6 +176,14 @@ inline bool fast_shape(int N, bool bwd, FastShape* fs) {
                             {256, 2, 16}, {512, 2, 32}, {1024, 2, 64}, {2048, 2, 128}};
   static const Row bw[] = {{384, 3, 16}, {768, 3, 32}, {1536, 2, 96}, {3072, 2, 192},
                            {256, 2, 16}, {512, 2, 32}, {1024, 2, 64}, {2048, 2, 128}};
+  if (bwd && (N == 1536 || N == 3072)) {   // A/B switch: 3 vectors per thread (fewer, fatter threads) for the wide backward
+    static const bool v3 = [] { const char* e = getenv("SB200_NA_BWD_VPT3"); return e && e[0] == '1'; }();
+    if (v3) {
+      fs->vpt = 3;
+      fs->tpr = N / 24;
+      return true;
+    }
+  }
   for (const Row& r : (bwd ? bw : fwd))
     if (r.N == N) {
       fs->vpt = r.vpt;

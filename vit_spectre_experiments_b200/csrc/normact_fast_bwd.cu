@@ -299,6 +299,7 @@ bool fast_bwd_launch(const Args& a0, size_t workspace_bytes, cudaStream_t st, in
   }
   SB200_SHAPE(3, 16, 16, 24) SB200_SHAPE(3, 32, 8, 12) SB200_SHAPE(2, 96, 4, 5) SB200_SHAPE(2, 192, 2, 2)
   SB200_SHAPE(2, 16, 16, 24) SB200_SHAPE(2, 32, 8, 12) SB200_SHAPE(2, 64, 4, 6) SB200_SHAPE(2, 128, 2, 3)
+  SB200_SHAPE(3, 64, 4, 6) SB200_SHAPE(3, 128, 2, 3)
 #undef SB200_SHAPE
   if (!fn) return false;
   Args a = a0;
