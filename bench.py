@@ -355,6 +355,9 @@ def main():
         nparam = sum(p.numel() for p in tr.model.parameters())
         hid, P, Cin = cfg.hidden_dim, cfg.patch_size, cfg.in_channels
         gemm_flops_img = 3 * 2 * (L * 2 * T * E * hid + (T - 1) * Cin * P * P * E + E * cfg.num_classes)
+        if getattr(cfg, "distill", False):   # frozen teacher forward (config 5): 12 E^2 MACs per token and layer + attention
+            Et, Lt, Tt = cfg.teacher_embed_dim, cfg.teacher_depth, T + 4     # DINOv3 ViT-B/16: cls + 4 storage tokens
+            gemm_flops_img += 2 * Lt * (12 * Et * Et * Tt + 2 * Tt * Tt * Et) + 2 * Et * cfg.num_classes
         own_bytes_step = sum(k["algo_bytes"] * k["launches"] for k in kernels.values()) / (min(K, 5) if args.cuda_graph else K)
         mem_bytes_step = own_bytes_step + batch * Cin * cfg.img_size ** 2 * 4 + nparam * 28
         tf_peak = peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1395.1))
