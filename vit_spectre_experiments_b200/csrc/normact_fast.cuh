@@ -176,9 +176,12 @@ inline bool fast_shape(int N, bool bwd, FastShape* fs) {
                             {256, 2, 16}, {512, 2, 32}, {1024, 2, 64}, {2048, 2, 128}};
   static const Row bw[] = {{384, 3, 16}, {768, 3, 32}, {1536, 2, 96}, {3072, 2, 192},
                            {256, 2, 16}, {512, 2, 32}, {1024, 2, 64}, {2048, 2, 128}};
-  if (bwd && (N == 1536 || N == 3072)) {   // A/B switch: 3 vectors per thread (fewer, fatter threads) for the wide backward
-    static const bool v3 = [] { const char* e = getenv("SB200_NA_BWD_VPT3"); return e && e[0] == '1'; }();
-    if (v3) {
+  if (bwd && (N == 1536 || N == 3072)) {
+    // the wide backward: 3 vectors per thread (384 fat threads, 168 registers) beat 2 (480 threads, 128 registers) --
+    // 1.009 vs 1.056 ms at N = 1536, 0.523 vs 0.572 ms at N = 3072 (profiles/r02_kernel_bench_na_v9_ab.txt): the per-row
+    // overhead is spread over 24 columns instead of 16.  SB200_NA_BWD_VPT3=0 selects the 2-vector shape.
+    static const bool v2 = [] { const char* e = getenv("SB200_NA_BWD_VPT3"); return e && e[0] == '0'; }();
+    if (!v2) {
       fs->vpt = 3;
       fs->tpr = N / 24;
       return true;
