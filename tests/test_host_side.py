@@ -227,3 +227,53 @@ def test_fft_module_matches_reference_golden():
     (gy,) = torch.autograd.grad((y * w).sum(), x)
     (gr,) = torch.autograd.grad((ref * w).sum(), x)
     assert (gy - gr).abs().max().item() < 1e-12
+
+
+def test_bench_reference_arm_contract():
+    """``bench.py --impl reference`` (the CPU arm the driver runs beside the GPU arm): one JSON line with the contract's
+    keys; ``kind`` is "reference" when the unmodified reference is installed under baseline/_ref, else "port"."""
+    import json
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--config", "c2",
+                        "--cpu-batch", "16", "--steps", "1", "--warmup", "1"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
+    d = json.loads(line)
+    assert d["impl"] == "reference" and d["unit"] == "images/s" and d["higher_is_better"] is True and d["value"] > 0
+    assert d["e2e"] == {"value": d["value"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    cb = d["cpu_baseline"]
+    have_ref = os.path.isdir(os.path.join(root, "baseline", "_ref", "spectre_vit"))
+    assert cb["kind"] == ("reference" if have_ref else "port") and cb["cores"] >= 1 and cb["value"] == d["value"]
+    assert d["config"]["workload"].startswith("Spectre-ViT tiny FFT-mix, MNIST")
+
+
+def test_reference_class_with_oracle_mixer_matches_mirror():
+    """With baseline/_ref present: the reference's OWN SpectreViT (oracle mixer in its slot, as bench.py's reference arm
+    builds it) and this repo's mirror with the same state produce the same logits on CPU."""
+    import pytest
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.isdir(os.path.join(root, "baseline", "_ref", "spectre_vit")):
+        pytest.skip("baseline/_ref not installed (run baseline/install_ref.sh)")
+    import sys
+    from types import SimpleNamespace
+
+    sys.path.insert(0, root)
+    import bench
+    from oracle.mixers_ref import OracleFFTMix
+    from vit_spectre_experiments_b200 import SpectreViT
+
+    cfg = SimpleNamespace(img_size=28, patch_size=4, in_channels=3, num_classes=10, embed_dim=16, num_encoders=2,
+                          num_heads=2, hidden_dim=24, dropout=0.0, activation="gelu", mixer="fft")
+    torch.manual_seed(0)
+    ref = bench.reference_model(cfg).eval()
+    mir = SpectreViT(img_size=28, patch_size=4, in_channels=3, num_classes=10, embed_dim=16, num_encoders=2, num_heads=2,
+                     hidden_dim=24, dropout=0.0, mixer=lambda d, t, h, o: OracleFFTMix(d, t, h, o)).eval()
+    mir.load_state_dict(ref.state_dict(), strict=True)
+    x = torch.randn(3, 3, 28, 28)
+    with torch.no_grad():
+        a, b = ref(x), mir(x)
+    assert (a - b).abs().max().item() <= 1e-5 * a.abs().max().item()
