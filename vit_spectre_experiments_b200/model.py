@@ -54,7 +54,28 @@ class SpectreLinear(nn.Module):
         )
         self.avg_pool = nn.Identity() if in_channels == out_channels else nn.AdaptiveAvgPool1d(out_channels)
 
+    def _kernel_ok(self, x: torch.Tensor) -> bool:
+        """CUDA, fused path on, widths the row-wise kernels take, and not inside the reference's fp16 autocast."""
+        if not (x.is_cuda and _FUSED_DEFAULT and x.dtype in (torch.float32, torch.bfloat16) and self.sparsity == 1):
+            return False
+        if torch.is_autocast_enabled() and torch.get_autocast_dtype("cuda") != torch.bfloat16:
+            return False
+        ok = getattr(self, "_na_ok", None)
+        if ok is None:
+            from . import _lib
+
+            ok = self._na_ok = _lib.load().spectre_norm_act_supported(self.out_channels, self.in_channels, 0) == 1
+        return ok
+
     def forward(self, x: torch.Tensor, dim=-1) -> torch.Tensor:
+        if self._kernel_ok(x):
+            # Linear (library GEMM) + ONE row-wise kernel for LayerNorm, GELU and the adaptive-pool skip (fp32 stream, as
+            # autocast's LayerNorm would give; deterministic backward -- the stock AdaptiveAvgPool1d backward uses atomics)
+            from .fused import norm_act
+
+            lin, ln = self.local_head[0], self.local_head[1]
+            h = F.linear(x, lin.weight, lin.bias).float()
+            return norm_act(h, ln.weight, ln.bias, skip=x.float(), eps=ln.eps, act="gelu")
         return self.local_head(x) + self.avg_pool(x)
 
 
