@@ -10,7 +10,7 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libspectre_b200.so")
+LIB_PATH = os.path.join(_HERE, os.environ.get("SB200_LIB_NAME", "libspectre_b200.so"))   # alternate name: A/B builds
 
 # every symbol include/spectre_b200.h declares
 EXPORTED_SYMBOLS = (

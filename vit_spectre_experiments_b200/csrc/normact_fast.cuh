@@ -13,6 +13,38 @@ namespace na {
 
 typedef unsigned long long u64;
 
+// Ring hand-back.  0 (default): the ring is consumed in groups of two row groups behind one CTA-wide barrier.
+// 1 (-DSB200_NA_ASYNC_RING=1): every warp returns a stage through a per-stage "empty" mbarrier as soon as it has read
+// it and thread 0 refills opportunistically (try_wait; it only blocks when its own next stage has not been issued yet):
+// no CTA-wide barrier inside the row loop, the rows of a CTA drift apart by up to the ring depth.  Measured SLOWER on
+// every shape (profiles/r02_kernel_bench_na_v10_ring_ab.txt: N = 1536 backward 1.117 vs 1.011 ms, forward 0.690 vs
+// 0.662 ms; LayerNorm forward 0.162 vs 0.154 ms; C4 step 75.6 vs 73.6 ms on the same box) -- as the barrier-free variant
+// of the round-1 kernels was: warps in lock step share the stage in L1 / shared memory and poll less.
+#ifndef SB200_NA_ASYNC_RING
+#define SB200_NA_ASYNC_RING 0
+#endif
+constexpr bool kAsyncRing = SB200_NA_ASYNC_RING != 0;
+
+// thread 0's refill state for the asynchronous ring
+struct RingProducer {
+  int next = 0;   // next iteration whose loads have not been issued
+  // issue everything that can be issued without blocking, up to S iterations ahead of `it`; the loads of `it` itself
+  // are waited for (their stage was last read S iterations ago by every warp: all of them get there without thread 0)
+  template <class Issue>
+  __device__ __forceinline__ void pump(int it, int n_it, int S, uint64_t* empty, Issue&& issue) {
+    while (next < n_it && next < it + S) {
+      const int s = next % S, use = next / S;
+      if (use > 0) {
+        const uint32_t parity = static_cast<uint32_t>(use - 1) & 1u;
+        if (next == it) ptx::mbar_wait(&empty[s], parity);
+        else if (!ptx::mbar_try_wait(&empty[s], parity)) break;
+      }
+      issue(next, s);
+      ++next;
+    }
+  }
+};
+
 __device__ __forceinline__ u64 pk(float lo, float hi) {
   u64 r;
   asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));

@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
   constexpr int NS = skip_width(MODE, N);
   static_assert(!contig_mode(MODE) || (MODE == kFastUp32 ? VPT == 3 : VPT == 2), "3:2 modes: 24 or 16 columns per thread");
   extern __shared__ __align__(128) uint8_t ring[];
-  __shared__ uint64_t full[kMaxStages];
+  __shared__ uint64_t full[kMaxStages], empty[kMaxStages];
   __shared__ float red[4][2][16];   // one slot per row group in flight between two CTA-wide barriers (x2: see row_sum2)
   __shared__ __align__(16) float sgb[2 * N];   // gamma, beta
   const int rg = threadIdx.x / TPR, t = threadIdx.x % TPR;
@@ -56,17 +56,24 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
   };
   pdl_launch_dependents();
   if (threadIdx.x == 0) {
-    for (int k = 0; k < S; ++k) ptx::mbar_init(&full[k], 1);
+    for (int k = 0; k < S; ++k) {
+      ptx::mbar_init(&full[k], 1);
+      ptx::mbar_init(&empty[k], blockDim.x / 32);   // one arrival per warp
+    }
     ptx::mbar_fence_init();
   }
+  RingProducer prod;
   pdl_wait();   // nothing above touches global memory
   const Seed sd = drop ? load_seed(a) : Seed{0u, 0u};
   // The ring is consumed in GROUPS of kGroup row groups: one CTA-wide barrier (and one refill round by thread 0) per
   // group instead of per row group -- barrier stalls were 1.0 of the ~5 stall cycles per issued instruction (ncu v7).
   // kGroup stages are being read, S - kGroup are in flight.
   constexpr int kGroup = 2;
-  if (threadIdx.x == 0)
-    for (int it = 0; it < S - kGroup && it < n_it; ++it) issue(it, it);
+  if (threadIdx.x == 0) {
+    if constexpr (kAsyncRing) prod.pump(0, n_it, S, empty, issue);
+    else
+      for (int it = 0; it < S - kGroup && it < n_it; ++it) issue(it, it);
+  }
   for (int i = threadIdx.x; i < N; i += NT) {
     sgb[i] = a.gamma[i];
     sgb[N + i] = a.beta[i];
@@ -92,10 +99,14 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
   uint32_t phase = 0;
   const uint8_t* st = ring;
   for (int it = 0; it < n_it; ++it, row += gstep) {
-    if (threadIdx.x == 0 && it % kGroup == 0) {   // the stages of the previous group are free (barrier below)
+    if (threadIdx.x == 0) {
+      if constexpr (kAsyncRing) {
+        prod.pump(it, n_it, S, empty, issue);
+      } else if (it % kGroup == 0) {   // the stages of the previous group are free (barrier below)
 #pragma unroll 1
-      for (int k = 0; k < kGroup; ++k)
-        if (it + S - kGroup + k < n_it) issue(it + S - kGroup + k, (it + S - kGroup + k) % S);
+        for (int k = 0; k < kGroup; ++k)
+          if (it + S - kGroup + k < n_it) issue(it + S - kGroup + k, (it + S - kGroup + k) % S);
+      }
     }
     const bool live = row < a.rows;
     const float mean = mean_n, rstd = rstd_n;
@@ -205,6 +216,10 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
                            bf_pack(ds[8 * q + 4], ds[8 * q + 5]), bf_pack(ds[8 * q + 6], ds[8 * q + 7]));
     }
     }
+    if constexpr (kAsyncRing) {   // dout / in0 are in registers now: the stage can be refilled
+      __syncwarp();
+      if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(&empty[stg]);
+    }
     float sa = hsum(s0), sb = hsum(s1);
     row_sum2<TPR>(sa, sb, red, it & 3, rg);
     if (live) {
@@ -222,11 +237,14 @@ __global__ void __launch_bounds__(TPR * RPC, 1) fast_bwd_kernel(const Args a) {
             make_uint4(bfpack2(dz[0]), bfpack2(dz[1]), bfpack2(dz[2]), bfpack2(dz[3]));
       }
     }
-    if (it % kGroup == kGroup - 1 || it + 1 == n_it) __syncthreads();   // group consumed
+    if constexpr (!kAsyncRing) {
+      if (it % kGroup == kGroup - 1 || it + 1 == n_it) __syncthreads();   // group consumed
+    }
     st += a.stage_bytes;
     if (++stg == S) { stg = 0; phase ^= 1u; st = ring; }
   }
   // ---- fold the row groups of the CTA in a fixed order (through the now idle ring, one accumulator kind at a time)
+  if constexpr (kAsyncRing) __syncthreads();   // every warp is past its last stage (and no bulk copy is in flight)
   float* fold = reinterpret_cast<float*>(ring);
   float* pg = a.part + static_cast<size_t>(blockIdx.x) * NACC * N;
 #pragma unroll

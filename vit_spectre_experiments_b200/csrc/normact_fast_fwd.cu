@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
   constexpr int NS = skip_width(MODE, N);
   static_assert(!contig_mode(MODE) || (MODE == kFastUp32 ? VPT == 3 : VPT == 2), "3:2 modes: 24 or 16 columns per thread");
   extern __shared__ __align__(128) uint8_t ring[];
-  __shared__ uint64_t full[kMaxStages];
+  __shared__ uint64_t full[kMaxStages], empty[kMaxStages];
   __shared__ float red[4][2][16];
   const int rg = threadIdx.x / TPR, t = threadIdx.x % TPR;
   const int S = a.stages;
@@ -53,15 +53,22 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
   };
   pdl_launch_dependents();
   if (threadIdx.x == 0) {
-    for (int k = 0; k < S; ++k) ptx::mbar_init(&full[k], 1);
+    for (int k = 0; k < S; ++k) {
+      ptx::mbar_init(&full[k], 1);
+      ptx::mbar_init(&empty[k], blockDim.x / 32);   // one arrival per warp
+    }
     ptx::mbar_fence_init();
   }
+  RingProducer prod;
   pdl_wait();   // nothing above touches global memory
   const Seed sd = drop ? load_seed(a) : Seed{0u, 0u};
   // the ring is consumed in groups of kGroup row groups: one CTA-wide barrier and one refill round per group
   constexpr int kGroup = 2;
-  if (threadIdx.x == 0)
-    for (int it = 0; it < S - kGroup && it < n_it; ++it) issue(it, it);
+  if (threadIdx.x == 0) {
+    if constexpr (kAsyncRing) prod.pump(0, n_it, S, empty, issue);
+    else
+      for (int it = 0; it < S - kGroup && it < n_it; ++it) issue(it, it);
+  }
   __syncthreads();
 
   const u64 c0 = splat(kGeluC0), c1 = splat(kGeluC1), c2 = splat(kGeluC2), half2 = splat(0.5f);
@@ -82,10 +89,14 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
   long long row = first0 + rg;
   const uint8_t* st = ring;
   for (int it = 0; it < n_it; ++it, row += gstep) {
-    if (threadIdx.x == 0 && it % kGroup == 0) {   // the stages of the previous group are free (barrier below)
+    if (threadIdx.x == 0) {
+      if constexpr (kAsyncRing) {
+        prod.pump(it, n_it, S, empty, issue);
+      } else if (it % kGroup == 0) {   // the stages of the previous group are free (barrier below)
 #pragma unroll 1
-      for (int k = 0; k < kGroup; ++k)
-        if (it + S - kGroup + k < n_it) issue(it + S - kGroup + k, (it + S - kGroup + k) % S);
+        for (int k = 0; k < kGroup; ++k)
+          if (it + S - kGroup + k < n_it) issue(it + S - kGroup + k, (it + S - kGroup + k) % S);
+      }
     }
     ptx::mbar_wait(&full[stg], phase);
     const bool live = row < a.rows;
@@ -188,7 +199,12 @@ __global__ void __launch_bounds__(fwd_threads(TPR), 2) fast_fwd_kernel(const Arg
         }
       }
     }
-    if (it % kGroup == kGroup - 1 || it + 1 == n_it) __syncthreads();   // the group is consumed: its stages may be refilled
+    if constexpr (kAsyncRing) {
+      __syncwarp();
+      if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(&empty[stg]);   // this warp is done with the stage
+    } else {
+      if (it % kGroup == kGroup - 1 || it + 1 == n_it) __syncthreads();   // the group is consumed: its stages may be refilled
+    }
     st += a.stage_bytes;
     if (++stg == S) { stg = 0; phase ^= 1u; st = ring; }
   }
