@@ -477,3 +477,23 @@ def test_training_step_is_cuda_graph_capturable(cuda_device, mixer, precision):
     assert len(set(ls)) == 3
     from vit_spectre_experiments_b200 import _lib
     _lib.graph_seed["tensor"] = None
+
+
+def test_patch_embed_folded_matrix_cache(cuda_device):
+    """Without autograd the folded matrix ``M`` is cached until a parameter changes (in-place update or
+    ``load_state_dict``); under autograd it is rebuilt so gradients reach the parameters."""
+    from vit_spectre_experiments_b200.model import SpectralPatchEmbed
+
+    torch.manual_seed(1)
+    m = SpectralPatchEmbed(32, 4, 64, 0.0, 3).to(cuda_device).eval()
+    img = torch.randn(2, 3, 32, 32, device=cuda_device)
+    with torch.no_grad():
+        y0 = m(img)
+        M0 = m._M
+        assert m(img) is not None and m._M is M0                    # second call: cache hit
+        m.freq_weight_h.mul_(1.5)                                    # in-place parameter update
+        y1 = m(img)
+        assert m._M is not M0 and not torch.equal(y0, y1)
+    y2 = m(img)                                                      # autograd on: fresh M with a graph
+    y2.sum().backward()
+    assert m.freq_weight_h.grad is not None and torch.allclose(y2, y1, rtol=1e-5, atol=1e-5)

@@ -283,6 +283,26 @@ class SpectralPatchEmbed(nn.Module):
             self._D = D   # plain attribute: not a buffer, so state_dict keys stay the reference's
         return D
 
+    def _folded_matrix(self, device, chans: int) -> torch.Tensor:
+        """``M [C*P*P, E]`` from the three parameters.  Under autograd it is rebuilt every call (the graph must reach the
+        parameters); without (evaluation, ``torch.no_grad``) it is cached until a parameter changes (in-place updates
+        bump ``_version``; ``load_state_dict`` copies in place)."""
+        P, half = self.P, self.P // 2 + 1
+        params = (self.proj.weight, self.freq_weight_h, self.freq_weight_w)
+        cacheable = not (torch.is_grad_enabled() and any(p.requires_grad for p in params))
+        key = (device, chans) + tuple((p.data_ptr(), p._version) for p in params)
+        if cacheable and getattr(self, "_M_key", None) == key:
+            return self._M
+        with torch.autocast("cuda", enabled=False):
+            wf = (self.proj.weight.float().view(self.embed_dim, chans, P, half)
+                  * self.freq_weight_h.float().view(1, 1, P, 1) * self.freq_weight_w.float().view(1, 1, 1, half))
+            # [C, P*P, P*half] @ [C, P*half, E] -> [C*P*P, E]
+            M = torch.matmul(self._cos_dft(device), wf.view(self.embed_dim, chans, P * half).permute(1, 2, 0))
+            M = M.reshape(chans * P * P, self.embed_dim)
+        if cacheable:
+            self._M, self._M_key = M.detach(), key
+        return M
+
     def forward_folded(self, img: torch.Tensor) -> torch.Tensor:
         """The same map as ONE GEMM: ``Re(rfft2)``, the frequency gains and the
         projection are all linear in the patch, so ``tokens = patch_flat @ M + b`` with
@@ -293,12 +313,7 @@ class SpectralPatchEmbed(nn.Module):
         batch, chans = img.shape[:2]
         P, half = self.P, self.P // 2 + 1
         nh, nw = img.shape[2] // P, img.shape[3] // P
-        with torch.autocast("cuda", enabled=False):
-            wf = (self.proj.weight.float().view(self.embed_dim, chans, P, half)
-                  * self.freq_weight_h.float().view(1, 1, P, 1) * self.freq_weight_w.float().view(1, 1, 1, half))
-            # [C, P*P, P*half] @ [C, P*half, E] -> [C*P*P, E]
-            M = torch.matmul(self._cos_dft(img.device), wf.view(self.embed_dim, chans, P * half).permute(1, 2, 0))
-            M = M.reshape(chans * P * P, self.embed_dim)
+        M = self._folded_matrix(img.device, chans)
         dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else img.dtype
         if (dt in (torch.float32, torch.bfloat16) and P % 4 == 0 and img.shape[3] % 4 == 0 and self.embed_dim % 8 == 0):
             # patch gather + cast | GEMM | cls / position / dropout pass: the CUDA kernels of csrc/embed.cu
