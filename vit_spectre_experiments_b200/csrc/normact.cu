@@ -88,11 +88,14 @@ __device__ __forceinline__ void st1(__nv_bfloat16* p, float v) { *p = __float2bf
 // one CTA-wide barrier (every row group of the CTA executes the same trip count); `slot` alternates so
 // consecutive calls need one barrier each.
 template <int NV>
-__device__ __forceinline__ void row_sum(float (&v)[NV], float (*red)[NV][8], int slot, int wpr, int rg) {
+__device__ __forceinline__ void row_sum(float (&v)[NV], float (*red)[NV][8], int slot, int wpr, int rg, int tpr = 32) {
+  // narrow rows (tpr = 8 or 16 threads: several rows per warp) only fold the lanes of their own aligned group
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1)
+    if (o < tpr) {
 #pragma unroll
-    for (int i = 0; i < NV; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+      for (int i = 0; i < NV; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+    }
   if (wpr > 1) {
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane == 0)
@@ -327,7 +330,7 @@ __global__ void __launch_bounds__(256, VPT == 3 ? 2 : 3) norm_act_fwd_kernel(con
         for (int e = 0; e < 8; ++e) z[i][e] = 0.f;
       }
     }
-    row_sum<2>(s, red, it & 1, wpr, rg);
+    row_sum<2>(s, red, it & 1, wpr, rg, tpr);
     const float dmean = s[0] * inv_n;
     const float mean = pivot + dmean;
     const float var = fmaxf(fmaf(-dmean, dmean, s[1] * inv_n), 0.f);
@@ -538,9 +541,9 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
       st8(myacc + j0, dg);
       st8(myacc + a.N + j0, db);
     }
-    row_sum<2>(s, red, it & 1, wpr, rg);
+    row_sum<2>(s, red, it & 1, wpr, rg, tpr);
     if constexpr (MODE == kSkipGeneral) {
-      if (wpr == 1) __syncwarp();   // one warp per row: dn is written and read by the same warp
+      if (wpr <= 1) __syncwarp();   // at most one warp per row: dn is written and read inside the same warp
       if (live)
         for (int u = t; u < (a.Ns >> 3); u += tpr) skip_general_bwd<T>(static_cast<T*>(a.d_skip) + row * a.Ns, dn, cov, u * 8, a.N <= a.Ns);
     }
@@ -645,7 +648,10 @@ static Shape launch_shape(int N, int Ns, bool has_in1, bool has_skip, int elem, 
                           int nacc = 2, bool general = false) {
   Shape sh{};
   const int nvec = N / 8;
-  if (nvec <= 32) { sh.vpt = 1; sh.tpr = 32; }
+  if (nvec <= 32) {   // one vector per thread; rows narrower than a warp share it (N = 48: 8 threads per row, 4 rows per warp)
+    sh.vpt = 1;
+    sh.tpr = nvec <= 8 ? 8 : nvec <= 16 ? 16 : 32;
+  }
   else {
     // 2 or 3 vectors per thread: fewest idle lanes first, then the larger count (fewer warps per row: cheaper
     // row sums, more work per thread between barriers)
