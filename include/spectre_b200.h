@@ -63,6 +63,19 @@ int spectre_fftmix_bwd(const void* dy, const void* x, const float* filt,
                        int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);
 size_t spectre_fftmix_bwd_workspace_bytes(int B, int H, int W, int E);
 
+/* FFT mixer backward that allocates nothing.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  Same kernels and results as spectre_fftmix_bwd; the scratch for the per-CTA partial filter
+ * gradients is a file-scope __device__ array of SPECTRE_NOALLOC_SCRATCH_BYTES inside the library (held by every
+ * GPU that loads it until the process exits) instead of a caller workspace.  Calls no cudaMalloc / cudaFree.
+ * Returns SPECTRE_E_WORKSPACE when spectre_fftmix_bwd_workspace_bytes(B,H,W,E) exceeds the array (12 MiB covers
+ * every compiled grid on a B200, e.g. 8.3 MB for the 14x14 ViT grids).  All calls share the array: calls on one
+ * stream are ordered, calls that overlap on the GPU (other streams, independent graph branches) RACE. */
+#define SPECTRE_NOALLOC_SCRATCH_BYTES (12u << 20)
+int spectre_fftmix_bwd_noalloc(const void* dy, const void* x, const float* filt,
+                               void* dx, float* dfilt,
+                               int B, int H, int W, int E, int has_cls, int act_dtype, void* stream);
+
 /* Haar DWT mixer forward (single-level orthonormal 2-D Haar over the token grid;
  * convention of DWTForward(wave="haar", mode="zero") at spectre_vit/repl/dwt_experiments.py:9,56;
  * mode names dwt_token/dwt_embed at spectre.py:33-34):

@@ -17,6 +17,7 @@ EXPORTED_SYMBOLS = (
     "spectre_fftmix_fwd",
     "spectre_fftmix_bwd",
     "spectre_fftmix_bwd_workspace_bytes",
+    "spectre_fftmix_bwd_noalloc",
     "spectre_dwtmix_fwd",
     "spectre_dwtmix_bwd",
     "spectre_dwtmix_bwd_workspace_bytes",
@@ -92,6 +93,8 @@ def load() -> ctypes.CDLL:
         lib.spectre_fftmix_bwd.restype = _i
         lib.spectre_fftmix_bwd_workspace_bytes.argtypes = [_i, _i, _i, _i]
         lib.spectre_fftmix_bwd_workspace_bytes.restype = _sz
+        lib.spectre_fftmix_bwd_noalloc.argtypes = [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_fftmix_bwd_noalloc.restype = _i
         lib.spectre_dwtmix_fwd.argtypes = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p]
         lib.spectre_dwtmix_fwd.restype = _i
         lib.spectre_dwtmix_bwd.argtypes = [_p, _p, _p, _p, _p, _p, _sz, _i, _i, _i, _i, _i, _i, _p]
