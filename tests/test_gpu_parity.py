@@ -48,6 +48,11 @@ FFT_CASES = [
     (9, 4, 4, 32, torch.float32),
     (1, 8, 8, 2, torch.float32),             # single channel pair
     (300, 14, 14, 64, torch.bfloat16),       # more image groups than CTAs in y
+    (5, 7, 7, 64, torch.float32),            # TMA-fed fp32 kernels: odd grid on 32-channel tiles
+    (33, 8, 8, 96, torch.float32),           # three exact 32-channel tiles, ragged image group
+    (6, 8, 8, 80, torch.float32),            # E % 32 != 0 on an even grid: 16-channel tiles
+    (6, 8, 8, 72, torch.float32),            # E % 16 != 0: first-generation kernel
+    (700, 4, 4, 32, torch.float32),          # ring wraps (more image groups than CTAs)
 ]
 
 
@@ -56,7 +61,7 @@ FFT_CASES = [
 def test_fftmix_fwd_bwd(cuda_device, B, H, W, E, dtype, has_cls):
     from vit_spectre_experiments_b200 import fft_mix
 
-    if not has_cls and B > 9:
+    if not has_cls and B > 9 and B != 33:
         pytest.skip("has_cls=False covered on the small cases")
     x, dy, filt = make(B, H, W, E, dtype, has_cls, 1234 + B + E, "fft")
     xd = x.to(cuda_device).requires_grad_(True)

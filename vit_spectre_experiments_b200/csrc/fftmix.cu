@@ -349,6 +349,14 @@ int fftmix_tc_bwd_dispatch(const void* dy, const void* x, const float* filt, voi
                            size_t ws_bytes, int B, int H, int W, int E, int cls, cudaStream_t st);
 size_t fftmix_tc_bwd_workspace(int B, int H, int W, int E);
 
+// TMA-fed in-place variants for fp32 activations live in fftmix_ring.cu (SB200_FFT_RING=0 keeps the kernels above).
+int fftmix_ring_supported(int H, int W, int E, const void* a, const void* b);
+int fftmix_ring_fwd_dispatch(const void* x, const float* filt, void* y, int B, int H, int W, int E, int cls,
+                             cudaStream_t st);
+int fftmix_ring_bwd_dispatch(const void* dy, const void* x, const float* filt, void* dx, float* dfilt, void* ws,
+                             size_t ws_bytes, int B, int H, int W, int E, int cls, cudaStream_t st);
+size_t fftmix_ring_bwd_workspace(int B, int H, int W, int E);
+
 // SB200_FFT_TC=0 keeps bf16 on the SIMT butterflies (A/B measurements); default is the tensor-core path.
 static bool tc_enabled() {
   static const bool on = [] {
@@ -362,6 +370,8 @@ int fftmix_fwd_dispatch(const void* x, const float* filt, void* y, int B, int H,
                         cudaStream_t st) {
   if (dtype == SPECTRE_DTYPE_BF16 && tc_enabled() && fftmix_tc_supported(H, W, E))
     return fftmix_tc_fwd_dispatch(x, filt, y, B, H, W, E, cls, st);
+  if (dtype == SPECTRE_DTYPE_F32 && fftmix_ring_supported(H, W, E, x, y))
+    return fftmix_ring_fwd_dispatch(x, filt, y, B, H, W, E, cls, st);
 #define F(h, w)                                                                                     \
   if (H == h && W == w)                                                                             \
     return dtype == SPECTRE_DTYPE_F32 ? fwd_launch<h, w, float>(x, filt, y, B, E, cls, st)          \
@@ -375,6 +385,8 @@ int fftmix_bwd_dispatch(const void* dy, const void* x, const float* filt, void* 
                         size_t ws_bytes, int B, int H, int W, int E, int cls, int dtype, cudaStream_t st) {
   if (dtype == SPECTRE_DTYPE_BF16 && tc_enabled() && fftmix_tc_supported(H, W, E))
     return fftmix_tc_bwd_dispatch(dy, x, filt, dx, dfilt, ws, ws_bytes, B, H, W, E, cls, st);
+  if (dtype == SPECTRE_DTYPE_F32 && fftmix_ring_supported(H, W, E, dy, x))
+    return fftmix_ring_bwd_dispatch(dy, x, filt, dx, dfilt, ws, ws_bytes, B, H, W, E, cls, st);
 #define F(h, w)                                                                                                      \
   if (H == h && W == w)                                                                                              \
     return dtype == SPECTRE_DTYPE_F32 ? bwd_launch<h, w, float>(dy, x, filt, dx, dfilt, ws, ws_bytes, B, E, cls, st) \
@@ -399,6 +411,8 @@ size_t fftmix_bwd_workspace(int B, int H, int W, int E) {
     const size_t t = fftmix_tc_bwd_workspace(B, H, W, E);
     if (t > need) need = t;
   }
+  const size_t r = fftmix_ring_bwd_workspace(B, H, W, E);
+  if (r > need) need = r;
   return need;
 }
 
