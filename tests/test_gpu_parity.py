@@ -53,6 +53,8 @@ FFT_CASES = [
     (6, 8, 8, 80, torch.float32),            # E % 32 != 0 on an even grid: 16-channel tiles
     (6, 8, 8, 72, torch.float32),            # E % 16 != 0: first-generation kernel
     (700, 4, 4, 32, torch.float32),          # ring wraps (more image groups than CTAs)
+    (67, 14, 14, 384, torch.float32),        # fp16-autocast fallback of ViT-S: one-channel lanes, 24 tiles
+    (40, 16, 16, 32, torch.float32),
 ]
 
 
