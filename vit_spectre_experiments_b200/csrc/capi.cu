@@ -47,6 +47,15 @@ int device_sm_count() {
   }
   return cached_sms > 0 ? cached_sms : 148;
 }
+void bind_primary_context() {
+  thread_local int bound = -1;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return;
+  if (dev != bound) {
+    cudaSetDevice(dev);
+    bound = dev;
+  }
+}
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 bool pdl_enabled() {

@@ -22,6 +22,10 @@ bool aligned16(const void* p);
 // cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE function attribute: set it on the first use of
 // (kernel, current device) -- a process driving several GPUs must not rely on a once-per-process flag.
 cudaError_t ensure_dynamic_smem(const void* kernel, int bytes);
+// The driver-API tensor-map encoder (cuTensorMapEncodeTiled) wants a context current on the calling thread; a thread that
+// has made no runtime-API call yet (an autograd worker) has none and gets CUDA_ERROR_INVALID_CONTEXT.  Binds the
+// primary context of the current device to this thread (cudaSetDevice; once per thread and device).
+void bind_primary_context();
 
 // ------------------------------------------------------------------ programmatic dependent launch
 // Every kernel here is enqueued with cudaLaunchAttributeProgrammaticStreamSerialization (launch_pdl) and runs

@@ -206,18 +206,28 @@ __device__ __forceinline__ void rows_inverse(const typename C::V* st, const RowP
   }
 }
 
-// The CLS token passes through the mixer unchanged (spectre.py:66 mixes the patch grid only).
+// The CLS token passes through the mixer unchanged (spectre.py:66 mixes the patch grid only).  Its G * kTileC floats
+// are loaded at the top of an iteration and stored at its end: a store right behind the load would park the warp for a
+// DRAM round trip in every iteration.
 template <class C>
-__device__ __forceinline__ void copy_cls(const float* __restrict__ src, float* __restrict__ dst, int b0, int B, int c0,
-                                         int E) {
-  for (int i = threadIdx.x; i < C::G * C::kTileC; i += C::NT) {
-    const int ch = i % C::kTileC, b = b0 + i / C::kTileC, c = c0 + ch;
-    if (b < B && c < E) {
-      const size_t off = static_cast<size_t>(b) * (C::HW + 1) * E + c;
-      __stcs(dst + off, __ldcs(src + off));
+struct ClsCopy {
+  static constexpr int kPer = (C::G * C::kTileC + C::NT - 1) / C::NT;
+  float v[kPer];
+  __device__ __forceinline__ void load(const float* __restrict__ src, int b0, int B, int c0, int E) {
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int i = threadIdx.x + k * C::NT, b = b0 + i / C::kTileC, c = c0 + i % C::kTileC;
+      if (i < C::G * C::kTileC && b < B && c < E) v[k] = __ldcs(src + static_cast<size_t>(b) * (C::HW + 1) * E + c);
     }
   }
-}
+  __device__ __forceinline__ void store(float* __restrict__ dst, int b0, int B, int c0, int E) const {
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int i = threadIdx.x + k * C::NT, b = b0 + i / C::kTileC, c = c0 + i % C::kTileC;
+      if (i < C::G * C::kTileC && b < B && c < E) __stcs(dst + static_cast<size_t>(b) * (C::HW + 1) * E + c, v[k]);
+    }
+  }
+};
 
 // ------------------------------------------------------------------ pipeline bookkeeping
 // One thread feeds the ring: iteration `it` of this CTA is image group blockIdx.y + it*gridDim.y, its tiles
@@ -278,7 +288,8 @@ __global__ void __launch_bounds__(C::NT, C::kMinBlocksFwd) fftmix_ring_fwd_kerne
   for (int it = 0; it < n_it; ++it) {
     V* st = feed.stage(it, 0);
     const int b0 = feed.image0(it);
-    if (cls) copy_cls<C>(x, y, b0, B, c0, E);
+    ClsCopy<C> cc;
+    if (cls) cc.load(x, b0, B, c0, E);
     feed.wait(it);
     rows_forward<C>(st, plan);
     __syncthreads();
@@ -324,6 +335,7 @@ __global__ void __launch_bounds__(C::NT, C::kMinBlocksFwd) fftmix_ring_fwd_kerne
     fence_proxy_async_smem();  // this stage is overwritten by the async proxy (TMA) later on
     __syncthreads();
     rows_inverse<C>(st, plan, y + static_cast<size_t>(b0) * img_floats, B - b0, E);
+    if (cls) cc.store(y, b0, B, c0, E);
   }
 }
 
@@ -373,7 +385,11 @@ __global__ void __launch_bounds__(C::NT, C::kMinBlocksBwd) fftmix_ring_bwd_kerne
     V* sy = feed.stage(it, 0);
     V* sx = feed.stage(it, 1);
     const int b0 = feed.image0(it);
-    if (cls) copy_cls<C>(dy, dx, b0, B, c0, E);
+    if (cls) {   // (backward: the iteration is long and registers are tight -- copied on the spot, measured faster)
+      ClsCopy<C> cc;
+      cc.load(dy, b0, B, c0, E);
+      cc.store(dx, b0, B, c0, E);
+    }
     feed.wait(it);
     rows_forward<C>(sy, plan);
     rows_forward<C>(sx, plan);
@@ -488,6 +504,7 @@ static EncodeTiledFn encode_fn() {
 static int make_map(CUtensorMap* map, const float* base, int B, int HW, int E, int cls, int chans, int G) {
   EncodeTiledFn enc = encode_fn();
   if (!enc) return fail(SPECTRE_E_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  bind_primary_context();
   const cuuint64_t dims[3] = {static_cast<cuuint64_t>(E), static_cast<cuuint64_t>(HW), static_cast<cuuint64_t>(B)};
   const cuuint64_t strides[2] = {static_cast<cuuint64_t>(E) * 4, static_cast<cuuint64_t>(HW + cls) * E * 4};
   const cuuint32_t box[3] = {static_cast<cuuint32_t>(chans), static_cast<cuuint32_t>(HW), static_cast<cuuint32_t>(G)};

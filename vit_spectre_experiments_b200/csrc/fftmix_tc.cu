@@ -614,6 +614,7 @@ static EncodeTiledFn encode_fn() {
 static int make_token_map(CUtensorMap* map, const void* base, int B, int HW, int T, int E, int cls) {
   EncodeTiledFn enc = encode_fn();
   if (!enc) return fail(SPECTRE_E_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  bind_primary_context();
   const cuuint64_t dims[3] = {static_cast<cuuint64_t>(E), static_cast<cuuint64_t>(HW), static_cast<cuuint64_t>(B)};
   const cuuint64_t strides[2] = {static_cast<cuuint64_t>(E) * 2, static_cast<cuuint64_t>(T) * E * 2};
   const cuuint32_t box[3] = {64, static_cast<cuuint32_t>(HW), 1};
