@@ -6,11 +6,14 @@
 // dwtmix_ml.cu keeps the tile in shared memory, one element per thread and access, a CTA barrier per level and
 // direction, 2-byte global loads for bf16: 13-31 % of the HBM peak (profiles/r01_kernel_bench_dwtml_v10.jsonl).  Here:
 //   * the tile [G images][H*W tokens][128 bytes of channels] arrives by ONE TMA box per tensor and iteration into a
-//     3-stage ring (cp.async.bulk.tensor + mbarrier) and LEAVES by a TMA store from the same slots;
+//     3-stage ring (cp.async.bulk.tensor + mbarrier); results leave straight from registers (bf16) or by a TMA store
+//     from the same slots (fp32) -- whichever measured faster, SB200_DWTML_STG=0/1 forces one;
 //   * a thread owns ONE channel of ONE image: it pulls its H*W values into registers (conflict-free: a warp reads 32
 //     adjacent channels of a token), runs all levels forward, multiplies by the weights, runs all levels back and
-//     writes its slots -- no thread ever reads another thread's element, so the only CTA barrier of an iteration
-//     is the one that hands the finished stage to the TMA store;
+//     stores -- no thread ever reads another thread's element, so the only CTA barrier of an iteration is the one
+//     that frees the stage for the next TMA load;
+//   * the weight tile is staged with its global loads batched ahead of their use (a dependent load -> scale -> store
+//     chain per element was 38 % of all stall samples of the first version: 32 serial L2 round trips per CTA);
 //   * butterflies are un-normalised (add / subtract only): a coefficient finalised at level l went through l halvings
 //     each way, so the weight tile in shared memory is pre-scaled by 4^-l (and the weight gradient once at the end);
 //   * the backward holds U x, U dy and the weight-gradient accumulators of its channel in registers (3 x 64).
@@ -41,24 +44,25 @@ template <> struct Io<__nv_bfloat16> {
   static __device__ __forceinline__ void st(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
 };
 
-template <int N_, class T_, int G_>
+template <int N_, class T_, int G_, int S_ = 3, int D_ = 0>
 struct Cfg {
+  static constexpr bool kDirectStore = D_ != 0;   // results leave by per-thread global stores instead of a TMA store
   using T = T_;
   static constexpr int N = N_, G = G_, HW = N * N;
   static constexpr int TC = 128 / static_cast<int>(sizeof(T));  // channels per tile: 128-byte token rows
   static constexpr int NT = G * TC;                             // one thread per (image slot, channel)
   static constexpr int kStageBytes = G * HW * TC * static_cast<int>(sizeof(T));  // per tensor
   static constexpr int kWgtBytes = HW * TC * 4;
-  static constexpr int S = 3;
+  static constexpr int S = S_;
   static_assert(kStageBytes % 128 == 0, "TMA slots stay 128-byte aligned");
   static constexpr size_t smem(int tensors) { return static_cast<size_t>(S) * tensors * kStageBytes + kWgtBytes + 128; }
 };
 
 // number of levels that touch grid point (r, q): it is a block corner of level l iff r, q are multiples of 2^(l-1)
+// (branch-free; grids here have at most 3 levels)
 __host__ __device__ inline int levels_of(int r, int q, int levels) {
-  int l = 1;
-  while (l < levels && (r % (1 << l)) == 0 && (q % (1 << l)) == 0) ++l;
-  return l;
+  const int rq = r | q;
+  return 1 + ((levels >= 2 && (rq & 1) == 0) ? 1 : 0) + ((levels >= 3 && (rq & 3) == 0) ? 1 : 0);
 }
 
 // one un-normalised level on the register grid; layout of the results as in dwtmix_ml.cu:
@@ -129,10 +133,26 @@ dwtml_reg_kernel(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
     mbar_fence_init();
     for (int s = 0; s < S; ++s) issue(s);
   }
-  for (int i = threadIdx.x; i < HW * TC; i += C::NT) {
-    const int pos = i / TC, c = c0 + i % TC;
-    const int l = levels_of(pos / N, pos % N, levels);
-    ws[i] = c < E ? __ldg(wgt + static_cast<size_t>(pos) * E + c) * (1.0f / static_cast<float>(1 << (2 * l))) : 0.f;
+  {   // weight tile -> shared memory, pre-scaled.  Loads in batches of 8 per thread BEFORE their first use: one at a
+      // time (a dependent load -> multiply -> store chain per element) cost 32 serial L2 round trips per CTA, 38 % of
+      // all stall samples of the kernel (profiles/r02_ncu_dwtml_v11.txt)
+    constexpr int kPer = HW * TC / C::NT, kBatch = kPer % 8 == 0 ? 8 : 4;
+    static_assert(HW * TC % C::NT == 0 && kPer % kBatch == 0, "weight tile splits evenly over the threads");
+#pragma unroll 1
+    for (int k0 = 0; k0 < kPer; k0 += kBatch) {
+      float wv[kBatch];
+#pragma unroll
+      for (int k = 0; k < kBatch; ++k) {
+        const int i = threadIdx.x + (k0 + k) * C::NT, pos = i / TC, cc = c0 + i % TC;
+        wv[k] = cc < E ? __ldg(wgt + static_cast<size_t>(pos) * E + cc) : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < kBatch; ++k) {
+        const int i = threadIdx.x + (k0 + k) * C::NT, pos = i / TC;
+        const int l = levels_of(pos / N, pos % N, levels);
+        ws[i] = wv[k] * (1.0f / static_cast<float>(1 << (2 * l)));
+      }
+    }
   }
   const int g = threadIdx.x / TC, c = threadIdx.x % TC;
   const int toff = g * HW * TC + c;   // element offset of this thread's (image slot, channel) in a stage
@@ -176,18 +196,28 @@ dwtml_reg_kernel(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
 #pragma unroll
     for (int i = 0; i < HW; ++i) v[i] *= ws[i * TC + c];
     inverse_levels<N>(v, levels);
+    if constexpr (C::kDirectStore) {
+      if (b0 + g < B) {
+        T* dst = out + static_cast<size_t>(b0 + g) * img_elems + static_cast<size_t>(cls) * E + c0 + c;
 #pragma unroll
-    for (int i = 0; i < HW; ++i) Io<T>::st(sa + toff + i * TC, v[i]);
-
-    fence_proxy_async_smem();   // generic-proxy writes above, async-proxy (TMA store) reads below
-    if (cls_live) out[cls_off] = cls_val;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      tma_store_3d(&tm_out, sa, c0, 0, b0);
-      tma_store_commit();
-      if (it >= 1) {
-        tma_store_wait_read<1>();   // every store but the one just issued has read its slots: stage (it-1) % S is free
-        issue(it - 1 + S);
+        for (int i = 0; i < HW; ++i) Io<T>::st(dst + static_cast<size_t>(i) * E, v[i]);
+      }
+      if (cls_live) out[cls_off] = cls_val;
+      __syncthreads();                       // every thread has read its slots: the stage is free
+      if (threadIdx.x == 0) issue(it + S);
+    } else {
+#pragma unroll
+      for (int i = 0; i < HW; ++i) Io<T>::st(sa + toff + i * TC, v[i]);
+      fence_proxy_async_smem();   // generic-proxy writes above, async-proxy (TMA store) reads below
+      if (cls_live) out[cls_off] = cls_val;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        tma_store_3d(&tm_out, sa, c0, 0, b0);
+        tma_store_commit();
+        if (it >= 1) {
+          tma_store_wait_read<1>();   // every store but the one just issued has read its slots: stage (it-1) % S is free
+          issue(it - 1 + S);
+        }
       }
     }
   }
@@ -317,15 +347,19 @@ int dwtml_reg_supported(int H, int W, int E, int dtype) {
 
 int dwtml_reg_launch(bool backward, const void* in, const void* xsave, const float* w, void* out, float* dw, void* ws,
                      size_t ws_bytes, int B, int H, int E, int cls, int levels, int dtype, int max_slabs,
-                     cudaStream_t st) {
+                     cudaStream_t st_) {
   using namespace mlreg;
-#define GO(n, T, g) return launch<Cfg<n, T, g>>(backward, in, xsave, w, out, dw, ws, ws_bytes, B, E, cls, levels, max_slabs, st)
+  // results leave by per-thread global stores (bf16: forward 0.0328 vs 0.0338 ms) or by a TMA store from the stage
+  // (fp32: 0.0524 / 0.0745 vs 0.0532 / 0.0767 ms); SB200_DWTML_STG=0/1 forces one; profiles/r02_kernel_bench_dwtml_v11.txt
+  static const int forced = [] { const char* e = getenv("SB200_DWTML_STG"); return e ? atoi(e) : -1; }();
+  const int direct = forced >= 0 ? forced : (dtype == SPECTRE_DTYPE_BF16 ? 1 : 0);
+#define GO(n, T, g)                                                                                                       \
+  return direct ? launch<Cfg<n, T, g, 3, 1>>(backward, in, xsave, w, out, dw, ws, ws_bytes, B, E, cls, levels, max_slabs, st_) \
+                : launch<Cfg<n, T, g, 3, 0>>(backward, in, xsave, w, out, dw, ws, ws_bytes, B, E, cls, levels, max_slabs, st_)
   if (dtype == SPECTRE_DTYPE_F32) {
     if (H == 8) GO(8, float, 4);
     GO(4, float, 4);
   }
-  static const int g4 = [] { const char* e = getenv("SB200_DWTML_G"); return e && e[0] == '4'; }();
-  if (H == 8 && g4) GO(8, __nv_bfloat16, 4);
   if (H == 8) GO(8, __nv_bfloat16, 2);
   GO(4, __nv_bfloat16, 2);
 #undef GO

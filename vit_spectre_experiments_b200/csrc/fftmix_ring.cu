@@ -109,30 +109,53 @@ struct Cfg {
 template <class C>
 __device__ __forceinline__ void load_filter(typename C::F* fcx, typename C::F* fre, const float* __restrict__ filt,
                                             int c0, int E, float scale) {
+  // All global loads of a batch are issued before their first use: one dependent load -> scale -> store chain per
+  // entry costs a serial L2 round trip each (11 per thread on the 14x14 grid).
   using F = typename C::F;
-  using O = VOps<typename C::V>;
+  using V = typename C::V;
+  using O = VOps<V>;
   constexpr int H = C::H, P = C::P, Wh = C::Wh;
-  for (int i = threadIdx.x; i < C::kFiltCx; i += C::NT) {
-    const int p = i % P, e = i / P, kw = e % C::NCX + 1, kh = e / C::NCX, c = c0 + C::VEC * p;
-    Cx<typename C::V> z = {O::zero(), O::zero()};
-    if (c < E) {
-      z = unpackf(ldfilt(filt + (static_cast<size_t>(kh * Wh + kw) * E + c) * 2, static_cast<F*>(nullptr)));
+  constexpr int kCx = (C::kFiltCx + C::NT - 1) / C::NT, kRe = (C::kFiltRe + C::NT - 1) / C::NT;
+  {
+    F raw[kCx];
+#pragma unroll
+    for (int k = 0; k < kCx; ++k) {
+      const int i = threadIdx.x + k * C::NT, p = i % P, e = i / P, kw = e % C::NCX + 1, kh = e / C::NCX;
+      const int c = c0 + C::VEC * p;
+      raw[k] = packf(Cx<V>{O::zero(), O::zero()});
+      if (i < C::kFiltCx && c < E)
+        raw[k] = ldfilt(filt + (static_cast<size_t>(kh * Wh + kw) * E + c) * 2, static_cast<F*>(nullptr));
+    }
+#pragma unroll
+    for (int k = 0; k < kCx; ++k) {
+      const int i = threadIdx.x + k * C::NT;
+      Cx<V> z = unpackf(raw[k]);
       z.re = O::muls(z.re, scale);
       z.im = O::muls(z.im, scale);
+      if (i < C::kFiltCx) fcx[i] = packf(z);
     }
-    fcx[i] = packf(z);
   }
-  for (int i = threadIdx.x; i < C::kFiltRe; i += C::NT) {
-    const int p = i % P, e = i / P, k = e % C::Hh, j = e / C::Hh, c = c0 + C::VEC * p;
-    const int kw = j == 0 ? 0 : C::W / 2, k2 = (H - k) % H;
-    Cx<typename C::V> z = {O::zero(), O::zero()};
-    if (c < E) {
-      const auto a = unpackf(ldfilt(filt + (static_cast<size_t>(k * Wh + kw) * E + c) * 2, static_cast<F*>(nullptr)));
-      const auto b = unpackf(ldfilt(filt + (static_cast<size_t>(k2 * Wh + kw) * E + c) * 2, static_cast<F*>(nullptr)));
+  {
+    F ra[kRe], rb[kRe];
+#pragma unroll
+    for (int k = 0; k < kRe; ++k) {
+      const int i = threadIdx.x + k * C::NT, p = i % P, e = i / P, kk = e % C::Hh, j = e / C::Hh;
+      const int c = c0 + C::VEC * p, kw = j == 0 ? 0 : C::W / 2, k2 = (H - kk) % H;
+      ra[k] = rb[k] = packf(Cx<V>{O::zero(), O::zero()});
+      if (i < C::kFiltRe && c < E) {
+        ra[k] = ldfilt(filt + (static_cast<size_t>(kk * Wh + kw) * E + c) * 2, static_cast<F*>(nullptr));
+        rb[k] = ldfilt(filt + (static_cast<size_t>(k2 * Wh + kw) * E + c) * 2, static_cast<F*>(nullptr));
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kRe; ++k) {
+      const int i = threadIdx.x + k * C::NT;
+      const Cx<V> a = unpackf(ra[k]), b = unpackf(rb[k]);
+      Cx<V> z;
       z.re = O::muls(O::add(a.re, b.re), 0.5f * scale);
       z.im = O::muls(O::sub(a.im, b.im), 0.5f * scale);
+      if (i < C::kFiltRe) fre[i] = packf(z);
     }
-    fre[i] = packf(z);
   }
 }
 
