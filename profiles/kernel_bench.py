@@ -20,6 +20,8 @@ try:
 except Exception:
     pass
 
+ML_LEVELS = int(os.environ.get("SB200_KB_LEVELS", "3"))   # levels of the multi-level Haar shapes (names say J3)
+
 SHAPES = [
     # name, kind, B, H, W, E, dtype
     ("C1 8x8 E512 f32 B8", "fft", 8, 8, 8, 512, torch.float32),
@@ -92,8 +94,8 @@ def main():
             fwd = lambda: _lib.check(lib.spectre_fftmix_fwd(x.data_ptr(), p.data_ptr(), y.data_ptr(), B, H, W, E, 1, code, st()), "fwd")
             bwd = lambda: _lib.check(lib.spectre_fftmix_bwd(dy.data_ptr(), x.data_ptr(), p.data_ptr(), dx.data_ptr(), dp.data_ptr(), ws.data_ptr(), nws, B, H, W, E, 1, code, st()), "bwd")
         elif kind == "dwtml":
-            fwd = lambda: _lib.check(lib.spectre_dwtmix_ml_fwd(x.data_ptr(), p.data_ptr(), y.data_ptr(), B, H, W, E, 1, 3, code, st()), "fwd")
-            bwd = lambda: _lib.check(lib.spectre_dwtmix_ml_bwd(dy.data_ptr(), x.data_ptr(), p.data_ptr(), dx.data_ptr(), dp.data_ptr(), ws.data_ptr(), nws, B, H, W, E, 1, 3, code, st()), "bwd")
+            fwd = lambda: _lib.check(lib.spectre_dwtmix_ml_fwd(x.data_ptr(), p.data_ptr(), y.data_ptr(), B, H, W, E, 1, ML_LEVELS, code, st()), "fwd")
+            bwd = lambda: _lib.check(lib.spectre_dwtmix_ml_bwd(dy.data_ptr(), x.data_ptr(), p.data_ptr(), dx.data_ptr(), dp.data_ptr(), ws.data_ptr(), nws, B, H, W, E, 1, ML_LEVELS, code, st()), "bwd")
         else:
             fwd = lambda: _lib.check(lib.spectre_dwtmix_fwd(x.data_ptr(), p.data_ptr(), y.data_ptr(), B, H, W, E, 1, code, st()), "fwd")
             bwd = lambda: _lib.check(lib.spectre_dwtmix_bwd(dy.data_ptr(), x.data_ptr(), p.data_ptr(), dx.data_ptr(), dp.data_ptr(), ws.data_ptr(), nws, B, H, W, E, 1, code, st()), "bwd")

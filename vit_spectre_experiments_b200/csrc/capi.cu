@@ -81,6 +81,38 @@ cudaError_t ensure_dynamic_smem(const void* kernel, int bytes) {
   return e;
 }
 
+int cached_blocks_per_sm(const void* kernel, int threads, size_t smem) {
+  struct Key {
+    const void* k;
+    int dev, threads;
+    size_t smem;
+    bool operator==(const Key& o) const { return k == o.k && dev == o.dev && threads == o.threads && smem == o.smem; }
+  };
+  struct Hash {
+    size_t operator()(const Key& a) const {
+      return std::hash<const void*>()(a.k) ^ (static_cast<size_t>(a.dev) * 0x9E3779B97F4A7C15ull) ^ (a.smem << 7) ^
+             static_cast<size_t>(a.threads);
+    }
+  };
+  static std::mutex mu;
+  static std::unordered_map<Key, int, Hash> memo;
+  Key key{kernel, 0, threads, smem};
+  cudaGetDevice(&key.dev);
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = memo.find(key);
+    if (it != memo.end()) return it->second;
+  }
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) {
+    cudaGetLastError();
+    return 1;   // not remembered: the attribute may not be set yet
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  memo[key] = per_sm;
+  return per_sm;
+}
+
 // out[i] = sum_k part[k][i], float4 granularity.  CTA = 64 float4 columns x 4 slab lanes; a lane strides over the
 // slabs with four independent accumulators (16 loads in flight per column), the lanes are combined through shared
 // memory in a fixed order => deterministic, and ~1 us instead of a serial chain of `slabs` L2 round trips.

@@ -26,6 +26,10 @@ cudaError_t ensure_dynamic_smem(const void* kernel, int bytes);
 // has made no runtime-API call yet (an autograd worker) has none and gets CUDA_ERROR_INVALID_CONTEXT.  Binds the
 // primary context of the current device to this thread (cudaSetDevice; once per thread and device).
 void bind_primary_context();
+// cudaOccupancyMaxActiveBlocksPerMultiprocessor, remembered per (kernel, device, threads, dynamic smem): the launchers
+// size their grids from it on every call, and the query costs a few microseconds of host time in front of kernels that
+// run for 20-80 us.
+int cached_blocks_per_sm(const void* kernel, int threads, size_t smem);
 
 // ------------------------------------------------------------------ programmatic dependent launch
 // Every kernel here is enqueued with cudaLaunchAttributeProgrammaticStreamSerialization (launch_pdl) and runs

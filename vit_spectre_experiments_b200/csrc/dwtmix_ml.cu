@@ -24,7 +24,7 @@ namespace sb200 {
 // register-resident variant for 4x4 / 8x8 grids (dwtmix_ml_reg.cu); SB200_DWTML_REG=0 keeps the kernels below
 int dwtml_reg_supported(int H, int W, int E, int dtype);
 int dwtml_reg_launch(bool backward, const void* in, const void* xsave, const float* w, void* out, float* dw, void* ws,
-                     size_t ws_bytes, int B, int H, int E, int cls, int levels, int dtype, int max_slabs,
+                     size_t ws_bytes, int B, int H, int E, int cls, int levels, int dtype, int max_slabs, int subband,
                      cudaStream_t st);
 
 namespace {
@@ -226,7 +226,7 @@ int spectre_dwtmix_ml_fwd(const void* x, const float* w, void* y, int B, int H, 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dwtml_reg_supported(H, W, E, act_dtype)) {
     const int rc = dwtml_reg_launch(false, x, nullptr, w, y, nullptr, nullptr, 0, B, H, E, has_cls, levels, act_dtype,
-                                    ml_slabs(B, E), st);
+                                    ml_slabs(B, E), 0, st);
     if (rc == SPECTRE_OK) last_error().clear();
     return rc;
   }
@@ -248,7 +248,7 @@ int spectre_dwtmix_ml_bwd(const void* dy, const void* x, const float* w, void* d
   const size_t wsb = workspace ? workspace_bytes : 0;
   if (dwtml_reg_supported(H, W, E, act_dtype)) {
     const int rc = dwtml_reg_launch(true, dy, x, w, dx, dw, workspace, wsb, B, H, E, has_cls, levels, act_dtype,
-                                    ml_slabs(B, E), st);
+                                    ml_slabs(B, E), 0, st);
     if (rc == SPECTRE_OK) last_error().clear();
     return rc;
   }

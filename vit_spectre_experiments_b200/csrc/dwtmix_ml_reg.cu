@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(C::NT, BWD ? 2 : 4)
 dwtml_reg_kernel(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_x,
                  const __grid_constant__ CUtensorMap tm_out, const typename C::T* __restrict__ in,
                  const float* __restrict__ wgt, typename C::T* __restrict__ out, float* __restrict__ part, int B, int E,
-                 int cls, int levels) {
+                 int cls, int levels, int subband) {
   using T = typename C::T;
   constexpr int N = C::N, HW = C::HW, TC = C::TC, G = C::G, S = C::S;
   constexpr int TENS = BWD ? 2 : 1;
@@ -111,6 +111,13 @@ dwtml_reg_kernel(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
   float* ws = reinterpret_cast<float*>(smem + static_cast<size_t>(S) * TENS * C::kStageBytes);  // [HW][TC], pre-scaled
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(S) * TENS * C::kStageBytes + C::kWgtBytes);
   const int c0 = blockIdx.x * TC;
+  // weight / weight-gradient row of grid point pos: in place on the lattice [H, W, E], or (single-level mixer of
+  // dwtmix.cu, levels == 1) sub-band major [4, H/2, W/2, E] with (ll, lowW/highH, highW/lowH, hh) = block points (a, c, b, d)
+  auto wrow = [&](int pos) {
+    if (!subband) return pos;
+    const int r = pos / N, q = pos % N;
+    return (((r & 1) + 2 * (q & 1)) * (N / 2) + (r >> 1)) * (N / 2) + (q >> 1);
+  };
   const int groups = (B + G - 1) / G;
   const int n_it = (groups - static_cast<int>(blockIdx.y) + static_cast<int>(gridDim.y) - 1) / static_cast<int>(gridDim.y);
   auto stage = [&](int it, int tensor) {
@@ -144,7 +151,7 @@ dwtml_reg_kernel(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
 #pragma unroll
       for (int k = 0; k < kBatch; ++k) {
         const int i = threadIdx.x + (k0 + k) * C::NT, pos = i / TC, cc = c0 + i % TC;
-        wv[k] = cc < E ? __ldg(wgt + static_cast<size_t>(pos) * E + cc) : 0.f;
+        wv[k] = cc < E ? __ldg(wgt + static_cast<size_t>(wrow(pos)) * E + cc) : 0.f;
       }
 #pragma unroll
       for (int k = 0; k < kBatch; ++k) {
@@ -239,7 +246,7 @@ dwtml_reg_kernel(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
 #pragma unroll
       for (int gg = 1; gg < G; ++gg) t += scr[gg * HW * TC + i];
       const int l = levels_of(pos / N, pos % N, levels);
-      slab[static_cast<size_t>(pos) * E + cc] = t * (1.0f / static_cast<float>(1 << (2 * l)));
+      slab[static_cast<size_t>(wrow(pos)) * E + cc] = t * (1.0f / static_cast<float>(1 << (2 * l)));
     }
   }
 }
@@ -284,9 +291,7 @@ static int slabs(int B, int E, int max_slabs) {
   auto kern = dwtml_reg_kernel<C, BWD>;
   const size_t smem = C::smem(BWD ? 2 : 1);
   ensure_dynamic_smem(reinterpret_cast<const void*>(kern), static_cast<int>(smem));
-  int per_sm = 1;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, C::NT, smem);
-  if (per_sm < 1) per_sm = 1;
+  const int per_sm = cached_blocks_per_sm(reinterpret_cast<const void*>(kern), C::NT, smem);
   const int tiles = E / C::TC, groups = (B + C::G - 1) / C::G;
   int ny = device_sm_count() * per_sm / tiles;
   if (ny < 1) ny = 1;
@@ -297,7 +302,7 @@ static int slabs(int B, int E, int max_slabs) {
 
 template <class C>
 static int launch(bool backward, const void* in, const void* xsave, const float* w, void* out, float* dw, void* ws,
-                  size_t ws_bytes, int B, int E, int cls, int levels, int max_slabs, cudaStream_t st) {
+                  size_t ws_bytes, int B, int E, int cls, int levels, int max_slabs, int subband, cudaStream_t st) {
   using T = typename C::T;
   // runtime-API calls first: they bind the primary context to this thread (an autograd worker may not have one yet),
   // which the driver-API tensor-map encoder needs (CUDA_ERROR_INVALID_CONTEXT otherwise)
@@ -310,7 +315,7 @@ static int launch(bool backward, const void* in, const void* xsave, const float*
   last_launch_count() = 1;
   if (!backward) {
     dwtml_reg_kernel<C, false><<<dim3(tiles, ny), C::NT, C::smem(1), st>>>(
-        tin, tx, tout, static_cast<const T*>(in), w, static_cast<T*>(out), nullptr, B, E, cls, levels);
+        tin, tx, tout, static_cast<const T*>(in), w, static_cast<T*>(out), nullptr, B, E, cls, levels, subband);
   } else {
     const size_t slab_floats = static_cast<size_t>(C::HW) * E;
     if (ny > 1 && ws_bytes < slab_floats * sizeof(float) * ny)
@@ -318,7 +323,7 @@ static int launch(bool backward, const void* in, const void* xsave, const float*
                   slab_floats * sizeof(float) * ny);
     float* part = ny > 1 ? static_cast<float*>(ws) : dw;
     dwtml_reg_kernel<C, true><<<dim3(tiles, ny), C::NT, C::smem(2), st>>>(
-        tin, tx, tout, static_cast<const T*>(in), w, static_cast<T*>(out), part, B, E, cls, levels);
+        tin, tx, tout, static_cast<const T*>(in), w, static_cast<T*>(out), part, B, E, cls, levels, subband);
     if (ny > 1) {
       launch_reduce_partials(part, dw, slab_floats, ny, st);
       last_launch_count() = 2;
@@ -345,8 +350,17 @@ int dwtml_reg_supported(int H, int W, int E, int dtype) {
   return E % (dtype == SPECTRE_DTYPE_F32 ? 32 : 64) == 0;
 }
 
+// image slabs (partial weight-gradient slabs) the backward would like for this shape
+int dwtml_reg_bwd_slabs(int B, int H, int E, int dtype) {
+  using namespace mlreg;
+  if (dtype == SPECTRE_DTYPE_F32)
+    return H == 8 ? slabs<Cfg<8, float, 4, 3, 0>, true>(B, E, 1 << 30) : slabs<Cfg<4, float, 4, 3, 0>, true>(B, E, 1 << 30);
+  return H == 8 ? slabs<Cfg<8, __nv_bfloat16, 2, 3, 1>, true>(B, E, 1 << 30)
+                : slabs<Cfg<4, __nv_bfloat16, 2, 3, 1>, true>(B, E, 1 << 30);
+}
+
 int dwtml_reg_launch(bool backward, const void* in, const void* xsave, const float* w, void* out, float* dw, void* ws,
-                     size_t ws_bytes, int B, int H, int E, int cls, int levels, int dtype, int max_slabs,
+                     size_t ws_bytes, int B, int H, int E, int cls, int levels, int dtype, int max_slabs, int subband,
                      cudaStream_t st_) {
   using namespace mlreg;
   // results leave by per-thread global stores (bf16: forward 0.0328 vs 0.0338 ms) or by a TMA store from the stage
@@ -354,8 +368,8 @@ int dwtml_reg_launch(bool backward, const void* in, const void* xsave, const flo
   static const int forced = [] { const char* e = getenv("SB200_DWTML_STG"); return e ? atoi(e) : -1; }();
   const int direct = forced >= 0 ? forced : (dtype == SPECTRE_DTYPE_BF16 ? 1 : 0);
 #define GO(n, T, g)                                                                                                       \
-  return direct ? launch<Cfg<n, T, g, 3, 1>>(backward, in, xsave, w, out, dw, ws, ws_bytes, B, E, cls, levels, max_slabs, st_) \
-                : launch<Cfg<n, T, g, 3, 0>>(backward, in, xsave, w, out, dw, ws, ws_bytes, B, E, cls, levels, max_slabs, st_)
+  return direct ? launch<Cfg<n, T, g, 3, 1>>(backward, in, xsave, w, out, dw, ws, ws_bytes, B, E, cls, levels, max_slabs, subband, st_) \
+                : launch<Cfg<n, T, g, 3, 0>>(backward, in, xsave, w, out, dw, ws, ws_bytes, B, E, cls, levels, max_slabs, subband, st_)
   if (dtype == SPECTRE_DTYPE_F32) {
     if (H == 8) GO(8, float, 4);
     GO(4, float, 4);

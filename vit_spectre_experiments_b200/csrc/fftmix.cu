@@ -268,9 +268,7 @@ struct Smem {
 // more slabs than image groups.
 template <class K>
 static int pick_slabs(K kernel, int threads, size_t smem, int tiles, int groups) {
-  int per_sm = 1;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem);
-  if (per_sm < 1) per_sm = 1;
+  const int per_sm = cached_blocks_per_sm(reinterpret_cast<const void*>(kernel), threads, smem);
   int ny = (device_sm_count() * per_sm) / tiles;
   if (ny < 1) ny = 1;
   if (ny > groups) ny = groups;
