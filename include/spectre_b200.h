@@ -158,6 +158,23 @@ int spectre_dwtmix_ml_bwd(const void* dy, const void* x, const float* w,
                           int B, int H, int W, int E, int has_cls, int levels, int act_dtype, void* stream);
 size_t spectre_dwtmix_ml_bwd_workspace_bytes(int B, int H, int W, int E);
 
+/* 1-D Haar mixers "dwt_token" (axis 0) / "dwt_embed" (axis 1): the two modes the reference's SpectreEncoderLayer
+ * docstring names -- "Wavelet transform in token dimension" / "in embedding dimension",
+ * spectre_vit/models/spectre/spectre.py:33-34 -- without code; defined here by analogy with the 2-D Haar mixer above:
+ * single-level orthonormal Haar along one axis of x[:, has_cls:, :] ([B, has_cls + N, E]), a learned real weight per
+ * coefficient, inverse Haar; the CLS row passes through.
+ *   axis 0: pairs of adjacent tokens per channel, w float32 [2, ceil(N/2), E] = (low, high); odd N: a zero token is
+ *           appended (mode="zero") and the result cropped
+ *   axis 1: pairs of adjacent channels per token, w float32 [2, N, E/2]
+ * Backward: dx = Haar(w * Haar(dy)), dw = sum_b Haar(x_b) * Haar(dy_b) (fully overwritten; partial slabs in the
+ * workspace, summed in a fixed order).  E a multiple of 8. */
+int spectre_haar1d_fwd(const void* x, const float* w, void* y,
+                       int B, int N, int E, int has_cls, int axis, int act_dtype, void* stream);
+int spectre_haar1d_bwd(const void* dy, const void* x, const float* w,
+                       void* dx, float* dw, void* workspace, size_t workspace_bytes,
+                       int B, int N, int E, int has_cls, int axis, int act_dtype, void* stream);
+size_t spectre_haar1d_bwd_workspace_bytes(int B, int N, int E, int axis);
+
 /* ---------------------------------------------------------------------------------------------------
  * MHPermutMix gather -- the reference's HEAD occupant of the slot (spectre_vit/models/spectre/layers.py:68-70):
  *   mixed[b, h, j] = x.view(B, T*E)[b, perms[h, j]] * signs[h, j]            -> [B, heads, F], F = T*E

@@ -239,6 +239,49 @@ def dwt_ml_mix_bwd_ref(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, H: in
     return torch.cat([dy[:, :1], dxg.reshape(B, H * W, E)], dim=1), (X * DY).sum(0)
 
 
+# ------------------------------------------------------------------ 1-D Haar mixers ("dwt_token" / "dwt_embed")
+# spectre_vit/models/spectre/spectre.py:33-34 names the two modes ("Wavelet transform in token dimension" / "in embedding
+# dimension") and the reference has no code for them: the operator is the 1-D analogue of dwt_mix_ref above -- parity
+# unpinned, like every Haar function of this file.
+def _haar1d_pairs(g: torch.Tensor, axis: str):
+    """(low, high) of the single-level orthonormal Haar along the token axis (odd count: a zero token appended,
+    mode="zero") or the embedding axis of ``g [B, N, E]``."""
+    r = 2.0 ** -0.5
+    if axis == "token":
+        gp = torch.nn.functional.pad(g, (0, 0, 0, g.shape[1] % 2))
+        a, b = gp[:, 0::2], gp[:, 1::2]
+    else:
+        a, b = g[..., 0::2], g[..., 1::2]
+    return (a + b) * r, (a - b) * r
+
+
+def _ihaar1d_pairs(lo: torch.Tensor, hi: torch.Tensor, axis: str, n_tokens: int) -> torch.Tensor:
+    r = 2.0 ** -0.5
+    a, b = (lo + hi) * r, (lo - hi) * r
+    if axis == "token":
+        B, P, E = a.shape
+        return torch.stack((a, b), dim=2).reshape(B, 2 * P, E)[:, :n_tokens]
+    B, N, P = a.shape
+    return torch.stack((a, b), dim=3).reshape(B, N, 2 * P)
+
+
+def haar1d_mix_ref(x: torch.Tensor, w: torch.Tensor, axis: str) -> torch.Tensor:
+    """y = cat(cls, IHaar(w * Haar(x[:, 1:]))) along ``axis`` in {"token", "embed"}.
+    w real ``[2, ceil(N/2), E]`` (token) or ``[2, N, E/2]`` (embed), ordered (low, high)."""
+    lo, hi = _haar1d_pairs(x[:, 1:], axis)
+    y = _ihaar1d_pairs(lo * w[0], hi * w[1], axis, x.shape[1] - 1)
+    return torch.cat([x[:, :1], y], dim=1)
+
+
+def haar1d_mix_bwd_ref(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, axis: str):
+    """Closed-form backward: the pair transform is orthogonal and symmetric (and crop^T = pad), so
+    dx = IHaar(w * Haar(dy)), dw = sum_b Haar(x_b) * Haar(dy_b)."""
+    dlo, dhi = _haar1d_pairs(dy[:, 1:], axis)
+    xlo, xhi = _haar1d_pairs(x[:, 1:], axis)
+    dxg = _ihaar1d_pairs(dlo * w[0], dhi * w[1], axis, x.shape[1] - 1)
+    return torch.cat([dy[:, :1], dxg], dim=1), torch.stack(((xlo * dlo).sum(0), (xhi * dhi).sum(0)))
+
+
 def haar2d_filterbank(g: torch.Tensor) -> torch.Tensor:
     """The same transform written as the published pywt/pytorch_wavelets Haar
     filter bank (``lo=[1,1]/sqrt2``, ``hi=[1,-1]/sqrt2``, stride 2, no padding

@@ -24,6 +24,9 @@ EXPORTED_SYMBOLS = (
     "spectre_dwtmix_ml_fwd",
     "spectre_dwtmix_ml_bwd",
     "spectre_dwtmix_ml_bwd_workspace_bytes",
+    "spectre_haar1d_fwd",
+    "spectre_haar1d_bwd",
+    "spectre_haar1d_bwd_workspace_bytes",
     "spectre_norm_act_fwd",
     "spectre_norm_act_bwd",
     "spectre_norm_act_bwd_workspace_bytes",
@@ -83,6 +86,12 @@ def load() -> ctypes.CDLL:
         lib.spectre_dwtmix_ml_bwd.restype = _i
         lib.spectre_dwtmix_ml_bwd_workspace_bytes.argtypes = [_i, _i, _i, _i]
         lib.spectre_dwtmix_ml_bwd_workspace_bytes.restype = _sz
+        lib.spectre_haar1d_fwd.argtypes = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_haar1d_fwd.restype = _i
+        lib.spectre_haar1d_bwd.argtypes = [_p, _p, _p, _p, _p, _p, _sz, _i, _i, _i, _i, _i, _i, _p]
+        lib.spectre_haar1d_bwd.restype = _i
+        lib.spectre_haar1d_bwd_workspace_bytes.argtypes = [_i, _i, _i, _i]
+        lib.spectre_haar1d_bwd_workspace_bytes.restype = _sz
         lib.spectre_debug_mark_main_kernel_end.argtypes = [_p]
         lib.spectre_debug_mark_main_kernel_end.restype = None
         lib.spectre_debug_mark_pending.argtypes = []

@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, os.environ.get("SB200_LIB_NAME", "libspectre_b200.so"))   # alternate name: A/B builds
 SOURCES = ["fftmix.cu", "fftmix_ring.cu", "fftmix_tc.cu", "dwtmix.cu", "normact.cu", "normact_fast_fwd.cu", "normact_fast_bwd.cu", "permut.cu", "embed.cu",
-           "dwtmix_ml.cu", "dwtmix_ml_reg.cu", "noalloc.cu", "capi.cu"]
+           "dwtmix_ml.cu", "dwtmix_ml_reg.cu", "haar1d.cu", "noalloc.cu", "capi.cu"]
 HEADERS = ["fft_codelets.cuh", "common.cuh", "sm100_ptx.cuh", "normact_common.cuh", "normact_fast.cuh", os.path.join("..", "..", "include", "spectre_b200.h")]
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

@@ -367,3 +367,71 @@ def dwt_mix_ml(x: torch.Tensor, weight: torch.Tensor, grid, has_cls: bool = True
     """
     H, W = grid
     return _DwtMl.apply(x, weight, int(H), int(W), bool(has_cls), int(levels))
+
+
+_HAAR1D_AXIS = {"token": 0, "embed": 1}
+
+
+def haar1d_weight_shape(n_tokens: int, embed_dim: int, axis: str):
+    """Shape of the float32 weight of ``haar1d_mix``: (low, high) sub-bands of the 1-D Haar along ``axis``."""
+    return (2, (n_tokens + 1) // 2, embed_dim) if axis == "token" else (2, n_tokens, embed_dim // 2)
+
+
+class _Haar1d(torch.autograd.Function):
+    """1-D Haar mixers ``dwt_token`` / ``dwt_embed`` (``spectre_haar1d_fwd/bwd``; mode names spectre.py:33-34)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, has_cls, axis):
+        lib = _lib.load()
+        what = f"haar1d_mix({axis})"
+        if axis not in _HAAR1D_AXIS:
+            raise RuntimeError(f"{what}: axis must be 'token' or 'embed'")
+        code = _act_code(x, what)
+        if x.dim() != 3 or x.shape[1] <= int(has_cls):
+            raise RuntimeError(f"{what}: expected x [B, {'1 + ' if has_cls else ''}N, E], got {tuple(x.shape)}")
+        B, T, E = x.shape
+        N = T - int(has_cls)
+        if E % 8:
+            raise RuntimeError(f"{what}: embed_dim must be a multiple of 8, got {E}")
+        want = haar1d_weight_shape(N, E, axis)
+        if weight.dtype != torch.float32 or tuple(weight.shape) != want:
+            raise RuntimeError(f"{what}: weight must be float32 {list(want)}, got {weight.dtype} {tuple(weight.shape)}")
+        x = x.contiguous()
+        w = weight.detach().contiguous()
+        y = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            with _timed("haar1d_fwd", (B, N, 1, E, x.element_size())):
+                rc = lib.spectre_haar1d_fwd(x.data_ptr(), w.data_ptr(), y.data_ptr(), B, N, E, int(has_cls),
+                                            _HAAR1D_AXIS[axis], code, _stream_ptr(x.device))
+        _lib.check(rc, "spectre_haar1d_fwd")
+        _lib.count_launches()
+        ctx.save_for_backward(x, w)
+        ctx.meta = (N, has_cls, axis)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _lib.load()
+        x, w = ctx.saved_tensors
+        N, has_cls, axis = ctx.meta
+        B, _, E = x.shape
+        dy = dy.to(x.dtype).contiguous()
+        dx, dw = torch.empty_like(x), torch.empty_like(w)
+        with torch.cuda.device(x.device):
+            nbytes = lib.spectre_haar1d_bwd_workspace_bytes(B, N, E, _HAAR1D_AXIS[axis])
+            ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
+            with _timed("haar1d_bwd", (B, N, 1, E, x.element_size())):
+                rc = lib.spectre_haar1d_bwd(dy.data_ptr(), x.data_ptr(), w.data_ptr(), dx.data_ptr(), dw.data_ptr(),
+                                            ws.data_ptr(), nbytes, B, N, E, int(has_cls), _HAAR1D_AXIS[axis],
+                                            _act_code(x, "haar1d_mix"), _stream_ptr(x.device))
+        _lib.check(rc, "spectre_haar1d_bwd")
+        _lib.count_launches()
+        return dx, dw, None, None
+
+
+def haar1d_mix(x: torch.Tensor, weight: torch.Tensor, has_cls: bool = True, axis: str = "token") -> torch.Tensor:
+    """``cat(cls, IHaar(weight * Haar(x[:, cls:])))`` with the single-level orthonormal 1-D Haar along the token axis
+    (``axis="token"``, the reference's ``dwt_token`` mode name) or the embedding axis (``"embed"``, ``dwt_embed``),
+    spectre.py:33-34; one fused CUDA pass.  weight float32 ``haar1d_weight_shape(N, E, axis)``; an odd token count is
+    zero-padded (``mode="zero"``) and cropped."""
+    return _Haar1d.apply(x, weight, bool(has_cls), str(axis))

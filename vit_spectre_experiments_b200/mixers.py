@@ -14,7 +14,7 @@ import math
 import torch
 import torch.nn as nn
 
-from .functional import dwt_mix, dwt_mix_ml, fft_mix
+from .functional import dwt_mix, dwt_mix_ml, fft_mix, haar1d_mix, haar1d_weight_shape
 
 
 def _resolve_grid(token_dim: int, grid, has_cls: bool):
@@ -155,6 +155,41 @@ class HaarDWTMix(_Fp32ParamMixin, nn.Module):
 
     def extra_repr(self) -> str:
         return f"embed_dim={self.embed_dim}, grid={self.grid}, has_cls={self.has_cls}"
+
+
+class Haar1dMix(_Fp32ParamMixin, nn.Module):
+    """Single-level 1-D Haar DWT along the token axis (``axis="token"``: the reference's ``dwt_token`` mode name) or the
+    embedding axis (``"embed"``: ``dwt_embed``) -> learned real weights per coefficient -> inverse (spectre.py:33-34 name
+    the modes; the reference has no code for them, the operator follows the 2-D ``HaarDWTMix``).
+
+    Parameter ``weight``: float32 ``[2, ceil(N/2), E]`` (token axis; N tokens without CLS, an odd N is zero-padded) or
+    ``[2, N, E/2]`` (embedding axis), ordered (low, high).  ``MHPermutMix`` ctor / forward contract."""
+
+    _fp32_param = "weight"
+
+    def __init__(self, embed_dim: int, token_dim: int, num_heads: int, out_channels: int, *, axis: str = "token",
+                 has_cls: bool = True, init_std: float = 0.02):
+        super().__init__()
+        if out_channels != embed_dim:
+            raise ValueError("Haar1dMix keeps the channel count: out_channels must equal embed_dim")
+        if axis not in ("token", "embed"):
+            raise ValueError(f"axis must be 'token' or 'embed', got {axis!r}")
+        if embed_dim % 8:
+            raise ValueError(f"Haar1dMix kernels need embed_dim % 8 == 0, got {embed_dim}")
+        self.embed_dim, self.token_dim, self.num_heads = embed_dim, token_dim, num_heads
+        self.axis, self.has_cls = axis, bool(has_cls)
+        n = token_dim - int(self.has_cls)
+        if n < 1:
+            raise ValueError(f"token_dim={token_dim} leaves no tokens to mix")
+        self.weight = nn.Parameter(1.0 + init_std * torch.randn(*haar1d_weight_shape(n, embed_dim, axis)))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        xa, out_dt = self._activation(x)
+        y = haar1d_mix(xa, self.weight, self.has_cls, self.axis)
+        return y if y.dtype == out_dt else y.to(out_dt)
+
+    def extra_repr(self) -> str:
+        return f"embed_dim={self.embed_dim}, token_dim={self.token_dim}, axis={self.axis}, has_cls={self.has_cls}"
 
 
 def _cos_sin(n: int):

@@ -25,9 +25,9 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .mixers import FNetMix, HaarDWTMix, SpectralFilterMix
+from .mixers import FNetMix, Haar1dMix, HaarDWTMix, SpectralFilterMix
 
-MIXERS = ("permut", "fft", "dwt", "fnet")
+MIXERS = ("permut", "fft", "dwt", "fnet", "dwt_token", "dwt_embed")
 
 # SB200_FUSED=0 keeps the stock torch composition of LayerNorm / GELU / pool / add around the mixer and
 # the GEMMs on CUDA too (A/B measurements); default: the fused norm_act kernels (fused.py).
@@ -130,6 +130,8 @@ def build_mixer(mixer: str, d_model: int, seq_length: int, nhead: int, grid=None
         return HaarDWTMix(d_model, seq_length, nhead, d_model, grid=grid)
     if mixer == "fnet":
         return FNetMix(d_model, seq_length, nhead, d_model)
+    if mixer in ("dwt_token", "dwt_embed"):   # mode names of the reference docstring (spectre.py:33-34)
+        return Haar1dMix(d_model, seq_length, nhead, d_model, axis=mixer[4:])
     raise ValueError(f"unknown mixer {mixer!r}; choose from {MIXERS}")
 
 
