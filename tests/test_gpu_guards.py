@@ -43,7 +43,11 @@ def _st(dev):
 
 @pytest.mark.parametrize("B,H,W,E,dt", [(5, 14, 14, 384, torch.bfloat16), (3, 14, 14, 200, torch.bfloat16),
                                         (7, 8, 8, 512, torch.bfloat16), (9, 7, 7, 48, torch.float32),
-                                        (3, 8, 8, 24, torch.float32), (301, 14, 14, 64, torch.bfloat16)])
+                                        (3, 8, 8, 24, torch.float32), (301, 14, 14, 64, torch.bfloat16),
+                                        # TMA-fed fp32 kernels: ragged image groups (images past B are zero-filled
+                                        # on load and must not be stored), one- and two-channel lanes
+                                        (33, 8, 8, 96, torch.float32), (5, 14, 14, 384, torch.float32),
+                                        (7, 4, 4, 32, torch.float32), (3, 16, 16, 16, torch.float32)])
 def test_fftmix_guards(cuda_device, B, H, W, E, dt):
     from vit_spectre_experiments_b200 import _lib
 
@@ -80,6 +84,52 @@ def test_dwtmix_guards(cuda_device, B, H, W, E, dt):
     _lib.check(lib.spectre_dwtmix_fwd(x.data_ptr(), w.data_ptr(), y.data_ptr(), B, H, W, E, 1, code, _st(cuda_device)), "fwd")
     _lib.check(lib.spectre_dwtmix_bwd(dy.data_ptr(), x.data_ptr(), w.data_ptr(), dx.data_ptr(), dw.data_ptr(), ws.data_ptr(),
                                       nws, B, H, W, E, 1, code, _st(cuda_device)), "bwd")
+    g.check()
+    assert torch.isfinite(y.float()).all() and torch.isfinite(dx.float()).all() and torch.isfinite(dw).all()
+
+
+@pytest.mark.parametrize("B,H,E,levels,dt", [(33, 8, 128, 3, torch.bfloat16), (5, 8, 64, 2, torch.float32),
+                                             (7, 4, 64, 2, torch.bfloat16), (3, 4, 32, 1, torch.float32),
+                                             (3, 8, 48, 3, torch.float32)])
+def test_dwtmix_ml_guards(cuda_device, B, H, E, levels, dt):
+    """Multi-level Haar: register / TMA kernel (E a multiple of the 128-byte tile) and the shared-memory kernel (E = 48)."""
+    from vit_spectre_experiments_b200 import _lib
+
+    lib, g = _lib.load(), Guarded(cuda_device)
+    W, T, code = H, H * H + 1, 0 if dt == torch.float32 else 1
+    x = torch.randn(B, T, E, device=cuda_device).to(dt)
+    dy = torch.randn(B, T, E, device=cuda_device).to(dt)
+    w = torch.randn(H, W, E, device=cuda_device)
+    y, dx = g.alloc((B, T, E), dt), g.alloc((B, T, E), dt)
+    dw = g.alloc((H, W, E), torch.float32)
+    nws = lib.spectre_dwtmix_ml_bwd_workspace_bytes(B, H, W, E)
+    ws = g.alloc((max(nws, 16),), torch.uint8)
+    _lib.check(lib.spectre_dwtmix_ml_fwd(x.data_ptr(), w.data_ptr(), y.data_ptr(), B, H, W, E, 1, levels, code,
+                                         _st(cuda_device)), "fwd")
+    _lib.check(lib.spectre_dwtmix_ml_bwd(dy.data_ptr(), x.data_ptr(), w.data_ptr(), dx.data_ptr(), dw.data_ptr(), ws.data_ptr(),
+                                         nws, B, H, W, E, 1, levels, code, _st(cuda_device)), "bwd")
+    g.check()
+    assert torch.isfinite(y.float()).all() and torch.isfinite(dx.float()).all() and torch.isfinite(dw).all()
+
+
+@pytest.mark.parametrize("B,N,E,dt", [(33, 49, 48, torch.float32), (5, 196, 384, torch.bfloat16), (300, 7, 8, torch.bfloat16)])
+@pytest.mark.parametrize("axis", [0, 1])
+def test_haar1d_guards(cuda_device, B, N, E, dt, axis):
+    from vit_spectre_experiments_b200 import _lib
+
+    lib, g = _lib.load(), Guarded(cuda_device)
+    T, code = N + 1, 0 if dt == torch.float32 else 1
+    x = torch.randn(B, T, E, device=cuda_device).to(dt)
+    dy = torch.randn(B, T, E, device=cuda_device).to(dt)
+    wshape = (2, (N + 1) // 2, E) if axis == 0 else (2, N, E // 2)
+    w = torch.randn(*wshape, device=cuda_device)
+    y, dx = g.alloc((B, T, E), dt), g.alloc((B, T, E), dt)
+    dw = g.alloc(wshape, torch.float32)
+    nws = lib.spectre_haar1d_bwd_workspace_bytes(B, N, E, axis)
+    ws = g.alloc((max(nws, 16),), torch.uint8)
+    _lib.check(lib.spectre_haar1d_fwd(x.data_ptr(), w.data_ptr(), y.data_ptr(), B, N, E, 1, axis, code, _st(cuda_device)), "fwd")
+    _lib.check(lib.spectre_haar1d_bwd(dy.data_ptr(), x.data_ptr(), w.data_ptr(), dx.data_ptr(), dw.data_ptr(), ws.data_ptr(),
+                                      nws, B, N, E, 1, axis, code, _st(cuda_device)), "bwd")
     g.check()
     assert torch.isfinite(y.float()).all() and torch.isfinite(dx.float()).all() and torch.isfinite(dw).all()
 
