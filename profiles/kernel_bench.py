@@ -35,6 +35,7 @@ SHAPES = [
     ("dwtml J3 8x8 E512 f32 B1024", "dwtml", 1024, 8, 8, 512, torch.float32),
     ("C4 14x14 E384 bf16 B256", "fft", 256, 14, 14, 384, torch.bfloat16),
     ("C4-shape 14x14 E384 f32 B256", "fft", 256, 14, 14, 384, torch.float32),
+    ("fp16-autocast ViT-S 14x14 E384 f32 B2048", "fft", 2048, 14, 14, 384, torch.float32),
     ("C5 14x14 E768 bf16 B128", "fft", 128, 14, 14, 768, torch.bfloat16),
     ("C4x4 14x14 E384 bf16 B1024", "fft", 1024, 14, 14, 384, torch.bfloat16),
     ("C4 bench 14x14 E384 bf16 B2048", "fft", 2048, 14, 14, 384, torch.bfloat16),
