@@ -193,3 +193,50 @@ def test_embed_guards(cuda_device):
     g.check()
     ref = img.reshape(B, C, 8, P, 8, P).permute(0, 2, 4, 1, 3, 5).reshape(B * n, C * P * P).bfloat16()
     assert torch.equal(A, ref)
+
+
+def test_tma_kernels_from_a_thread_without_a_cuda_context(cuda_device):
+    """The TMA-fed kernels encode their tensor maps with the driver API, which needs a context current on the calling
+    thread; a thread that has made no runtime-API call yet (an autograd worker, a serving thread) has none.  The C ABI
+    binds the primary context itself (`bind_primary_context`): calls made from a brand-new thread must succeed even
+    when everything the launcher would query is already cached."""
+    import threading
+
+    from vit_spectre_experiments_b200 import _lib
+
+    lib = _lib.load()
+    dev = cuda_device
+    B, E = 6, 64
+    jobs = []
+    for (H, dt) in ((8, torch.float32), (14, torch.bfloat16), (8, torch.bfloat16)):
+        T, code = H * H + 1, 0 if dt == torch.float32 else 1
+        x = torch.randn(B, T, E, device=dev).to(dt)
+        f = torch.randn(H, H // 2 + 1, E, 2, device=dev)
+        w = torch.randn(H, H, E, device=dev)
+        y, y2 = torch.empty_like(x), torch.empty_like(x)
+        jobs.append((H, code, x, f, w, y, y2))
+    st = _st(dev)
+
+    def run(results):
+        for (H, code, x, f, w, y, y2) in jobs:
+            results.append(lib.spectre_fftmix_fwd(x.data_ptr(), f.data_ptr(), y.data_ptr(), B, H, H, E, 1, code, st))
+            if H == 8:
+                results.append(lib.spectre_dwtmix_ml_fwd(x.data_ptr(), w.data_ptr(), y2.data_ptr(), B, H, H, E, 1, 3, code, st))
+
+    warm = []
+    run(warm)                       # main thread: fills the per-kernel caches
+    torch.cuda.synchronize()
+    ref = [(j[5].clone(), j[6].clone()) for j in jobs]
+    for j in jobs:
+        j[5].zero_(); j[6].zero_()
+    torch.cuda.synchronize()
+    res = []
+    t = threading.Thread(target=run, args=(res,))
+    t.start(); t.join()
+    torch.cuda.synchronize()
+    assert warm and all(rc == 0 for rc in warm), warm
+    assert res and all(rc == 0 for rc in res), (res, lib.spectre_last_error().decode())
+    for j, (ya, yb) in zip(jobs, ref):
+        assert torch.equal(j[5], ya)
+        if j[0] == 8:
+            assert torch.equal(j[6], yb)
