@@ -166,6 +166,20 @@ __device__ __forceinline__ void skip_general_bwd(T* drow, const float* dn, const
   st8(drow + c0, g);
 }
 
+// the same, one skip column per lane: for N > Ns (a skip column feeds ceil(N / Ns) + 1 outputs) the vector form above
+// runs 8 runtime-length loops per lane on Ns / 8 lanes of the row -- 43 % of the executed instructions of the C2 backward
+// (N = 256, Ns = 48: 6 busy lanes of 32, profiles/r02_ncu_src_top_v11.txt); here every lane of the row takes columns
+template <class T>
+__device__ __forceinline__ void skip_general_bwd_cols(T* drow, const float* dn, const unsigned* cov, int t, int tpr, int Ns) {
+  for (int c = t; c < Ns; c += tpr) {
+    const unsigned w = cov[c];
+    const int s = static_cast<int>(w & 0xffffu), n = static_cast<int>(w >> 16);
+    float acc = dn[s];
+    for (int k = 1; k < n; ++k) acc += dn[s + k];
+    st1(drow + c, acc);
+  }
+}
+
 // o[0..8) += pool(skip)[j0 .. j0+8) for integer ratios resolved at compile time
 template <class T, int K>
 __device__ __forceinline__ void skip_up_add(const T* srow, int j0, float (&o)[8]) {
@@ -544,8 +558,13 @@ __global__ void __launch_bounds__(256, 3) norm_act_bwd_kernel(const Args a) {
     row_sum<2>(s, red, it & 1, wpr, rg, tpr);
     if constexpr (MODE == kSkipGeneral) {
       if (wpr <= 1) __syncwarp();   // at most one warp per row: dn is written and read inside the same warp
-      if (live)
-        for (int u = t; u < (a.Ns >> 3); u += tpr) skip_general_bwd<T>(static_cast<T*>(a.d_skip) + row * a.Ns, dn, cov, u * 8, a.N <= a.Ns);
+      if (live) {
+        if (a.N <= a.Ns) {
+          for (int u = t; u < (a.Ns >> 3); u += tpr) skip_general_bwd<T>(static_cast<T*>(a.d_skip) + row * a.Ns, dn, cov, u * 8, true);
+        } else {
+          skip_general_bwd_cols<T>(static_cast<T*>(a.d_skip) + row * a.Ns, dn, cov, t, tpr, a.Ns);
+        }
+      }
     }
     if (live) {
       const float m1 = s[0] * inv_n, m2 = s[1] * inv_n;
