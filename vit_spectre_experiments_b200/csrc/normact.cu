@@ -168,7 +168,7 @@ __device__ __forceinline__ void skip_general_bwd(T* drow, const float* dn, const
 
 // the same, one skip column per lane: for N > Ns (a skip column feeds ceil(N / Ns) + 1 outputs) the vector form above
 // runs 8 runtime-length loops per lane on Ns / 8 lanes of the row -- 43 % of the executed instructions of the C2 backward
-// (N = 256, Ns = 48: 6 busy lanes of 32, profiles/r02_ncu_src_top_v11.txt); here every lane of the row takes columns
+// (N = 256, Ns = 48: 6 busy lanes of 32, profiles/r02_ncu_src_c2_v13.txt); here every lane of the row takes columns
 template <class T>
 __device__ __forceinline__ void skip_general_bwd_cols(T* drow, const float* dn, const unsigned* cov, int t, int tpr, int Ns) {
   for (int c = t; c < Ns; c += tpr) {
